@@ -1,0 +1,190 @@
+"""Training engine (the body of the reference's ``main()``, /root/reference/main.py:49-185).
+
+Flow kept from the reference: build data -> ``initialize_model`` -> Adam(lr=LR) ->
+optional resume -> weight sync from rank 0 -> per epoch {train over the shard with
+CE loss; rank 0 checkpoints and (optionally) validates} with the same log lines
+(``_Epoch: {} | Train Loss: {} | Time: {}``, ``_Epoch: {} | Acc: {}``).
+
+Changed underneath: device-resident bf16 channels-last activations, on-device synthetic
+shards (or GPU-preprocessed files), gradients reduced bucket-by-bucket *during*
+backward by the fused peer-memory all-reduce+Adam kernel, CUDA-event timing reported as
+max over ranks, resume continues from the stored epoch, Inception's aux
+loss handled (D2), frozen parameters allowed (D1), logged loss additionally all-reduced
+(D9), validation does not stall the other ranks (they wait at a barrier instead of
+inside an Allreduce, D8).
+"""
+from __future__ import annotations
+
+import os
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+from ..data.synthetic import SyntheticShard
+from ..models import initialize_model
+from ..parallel import bootstrap
+from ..parallel.collectives import Hyper
+from ..parallel.ddp import FusedDataParallel
+from ..utils.config import Settings, image_hw
+from ..utils.logging import get_logger
+from ..utils.timing import DeviceTimer, max_over_ranks
+from .checkpoint import checkpoint_path, load_checkpoint, make_checkpoint, save_checkpoint
+
+
+def compute_dtype(settings: Settings, device: torch.device) -> torch.dtype:
+    if device.type == "cuda" and settings.DTYPE == "bf16":
+        return torch.bfloat16
+    return torch.float32
+
+
+def loss_from_outputs(outputs: Any, labels: torch.Tensor) -> torch.Tensor:
+    """CE on the main head (+0.4 x CE on Inception's aux head when it exists)."""
+    if isinstance(outputs, tuple):
+        logits, aux = outputs[0], outputs[1]
+        loss = ops.cross_entropy(logits, labels)
+        if aux is not None:
+            loss = loss + 0.4 * ops.cross_entropy(aux, labels)
+        return loss
+    return ops.cross_entropy(outputs, labels)
+
+
+class Trainer:
+    """One model replica + its DP engine.  ``train_step`` is the hot loop body of main.py:146-156."""
+
+    def __init__(self, settings: Settings, world: Optional[bootstrap.World] = None, model: Optional[nn.Module] = None):
+        self.s = settings
+        self.world = world or bootstrap.init_world(settings.DEVICE)
+        self.device = self.world.device
+        self.dtype = compute_dtype(settings, self.device)
+        self.log = get_logger()
+        torch.manual_seed(settings.SEED)
+        if model is None:
+            model, self.input_size = initialize_model(settings.MODEL_NAME, settings.NUM_CLASSES,
+                                                      settings.FEATURE_EXTRACT, use_pretrained=settings.USE_PRETRAINED)
+        else:
+            self.input_size = 224
+        self.hw = image_hw(settings, self.input_size)
+        self.channels_last = self.device.type == "cuda"
+        if self.channels_last:
+            model = model.to(memory_format=torch.channels_last)
+        self.model = model
+        hyper = Hyper(kind=settings.OPTIMIZER, lr=settings.LR, momentum=settings.MOMENTUM)
+        shadow = torch.bfloat16 if (self.dtype == torch.bfloat16 and ops.native_enabled()) else None
+        self.engine = FusedDataParallel(model, self.world, hyper, bucket_mb=settings.BUCKET_MB,
+                                        algo=settings.ALLREDUCE_ALGO, shadow_dtype=shadow)
+        self.optimizer = self.engine.optimizer
+        self.start_epoch = 0
+        self.autocast = (self.dtype == torch.bfloat16 and not ops.native_enabled())
+
+    # ------------------------------------------------------------------ set-up helpers
+    def maybe_resume(self) -> None:
+        if self.s.FROM_CHECKPOINT:
+            path = os.path.join(self.s.CHECKPOINT_DIR, self.s.CHECKPOINT_NAME)
+            self.log.info("_Loading Checkpoint")
+            _, _, epoch = load_checkpoint(path, self.model, self.optimizer, map_location=self.device)
+            self.start_epoch = epoch + 1
+            self.log.info("_Checkpoint loaded")
+
+    def sync_params(self) -> None:
+        self.engine.sync_params(0)
+
+    def make_shard(self, total: Optional[int] = None, shuffle: bool = True, all_ranks: bool = True) -> SyntheticShard:
+        if total is None:
+            total = self.s.SYNTHETIC_SAMPLES or (800 if self.s.DEBUG else 40000)   # main.py:73-82 sizes
+        r, w = (self.world.rank, self.world.size) if all_ranks else (0, 1)
+        return SyntheticShard(total, self.s.BATCH_SIZE, self.s.NUM_CLASSES, self.hw, r, w, self.s.SEED, self.device,
+                              self.dtype, self.channels_last, shuffle)
+
+    # ------------------------------------------------------------------ hot loop
+    def forward_loss(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        if self.autocast:
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                out = self.model(images)
+            if isinstance(out, tuple):
+                out = tuple(o.float() if o is not None else None for o in out)
+            else:
+                out = out.float()
+            return loss_from_outputs(out, labels)
+        return loss_from_outputs(self.model(images), labels)
+
+    def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """fwd -> CE -> zero_grad -> backward (buckets reduce+update as they complete) -> join."""
+        loss = self.forward_loss(images, labels)
+        self.optimizer.zero_grad()
+        loss.backward()
+        self.optimizer.step()
+        return loss.detach()
+
+    @torch.no_grad()
+    def evaluate(self, shard: SyntheticShard) -> float:
+        """Rank-local accuracy pass (main.py:173-185): argmax, compare, count."""
+        self.model.eval()
+        correct = torch.zeros((), dtype=torch.int64, device=self.device)
+        n = 0
+        for images, labels in shard:
+            if self.autocast:
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    out = self.model(images)
+            else:
+                out = self.model(images)
+            correct += ops.count_correct(out, labels)
+            n += labels.numel()
+        self.model.train()
+        return float(correct.item()) / max(n, 1)
+
+    # ------------------------------------------------------------------ the epoch loop
+    def fit(self, train: Optional[SyntheticShard] = None, val: Optional[SyntheticShard] = None,
+            epochs: Optional[int] = None) -> List[Dict[str, float]]:
+        s, log, w = self.s, self.log, self.world
+        train = train or self.make_shard()
+        log.info("_Files Received: {}".format(train.num_samples))
+        if val is None and s.VALIDATE and w.rank == 0:
+            val = self.make_shard(total=train.total, shuffle=False, all_ranks=False)   # the un-sharded sample, main.py:108
+        log.info("_Model Created: {}".format(s.MODEL_NAME))
+        self.maybe_resume()
+        self.sync_params()
+        log.info("_Model loaded to {}".format(str(self.device).upper()))
+        log.info("_Entering training Loop")
+        history: List[Dict[str, float]] = []
+        n_epochs = s.NUM_EPOCHS if epochs is None else epochs
+        for epoch in range(self.start_epoch, n_epochs):
+            self.model.train()
+            train.set_epoch(epoch)
+            tr_loss = torch.zeros((), dtype=torch.float32, device=self.device)
+            with DeviceTimer(self.device) as t:
+                for images, labels in train:
+                    tr_loss += self.train_step(images, labels).float()
+            nb = max(len(train), 1)
+            local = float(tr_loss.item()) / nb
+            secs = max_over_ranks(t.ms, self.device if w.backend == "nccl" else "cpu") / 1e3
+            log.info("_Epoch: {} | Train Loss: {} | Time: {}".format(epoch, local, secs))
+            rec = {"epoch": epoch, "loss": local, "time_s": secs,
+                   "img_per_s": train.num_samples * w.size / max(secs, 1e-9)}
+            if w.rank == 0:
+                log.info("_Creating a checkpoint at epoch {}".format(epoch))
+            ck = make_checkpoint(epoch, self.model, self.optimizer, local)       # collective (gathers sliced state)
+            if w.rank == 0:
+                save_checkpoint(ck, epoch, s.MODEL_NAME, s.CHECKPOINT_DIR, s.MODELS_DIR)
+                log.info("_Checkpoint saved")
+                if s.VALIDATE and val is not None:
+                    log.info("_Evaluating model")
+                    rec["acc"] = self.evaluate(val)
+                    log.info("_Epoch: {} | Acc: {}".format(epoch, rec["acc"]))
+            if w.size > 1:
+                import torch.distributed as dist
+                dist.barrier()
+            history.append(rec)
+        return history
+
+    def close(self) -> None:
+        self.engine.close()
+
+
+def run_training(settings: Settings, world: Optional[bootstrap.World] = None) -> List[Dict[str, float]]:
+    tr = Trainer(settings, world)
+    try:
+        return tr.fit()
+    finally:
+        tr.close()

@@ -1,0 +1,167 @@
+"""Reference-shaped communication helpers (``mpi_tools.py`` surface).
+
+Function names and meanings follow /root/reference/mpi_tools.py:5-53 --
+``num_processes``, ``mpi_all_reduce``, ``mpi_sum``, ``mpi_avg_grads``, ``mpi_broadcast``,
+``sync_params`` -- but they are thin fronts over the flat-arena runtime: one bucketed
+reduction instead of one blocking ``MPI.Allreduce`` per tensor, tensors stay on the
+device, and frozen parameters (``grad is None``) are skipped instead of crashing
+(SURVEY D1).  They work for *any* ``nn.Module`` + *any* torch optimizer, i.e. a user
+can keep the reference's hand-written training loop unchanged.  The fully fused path
+(reduce + Adam in one kernel, overlapped with backward) is ``parallel.ddp``.
+"""
+from __future__ import annotations
+
+import weakref
+from typing import Any, Dict, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import bootstrap
+from .arena import FlatLayout, alloc_arena
+from .collectives import make_collectives
+
+SUM = "sum"
+_COLL: Dict[int, Any] = {}
+_AVERAGERS: "weakref.WeakKeyDictionary[nn.Module, _GradAverager]" = weakref.WeakKeyDictionary()
+
+
+def _collectives():
+    w = bootstrap.world()
+    key = id(w)
+    if key not in _COLL:
+        _COLL.clear()
+        _COLL[key] = make_collectives(w)
+    return _COLL[key]
+
+
+def reset() -> None:
+    """Drop cached arenas/backends (tests; world re-initialisation)."""
+    for c in _COLL.values():
+        c.close()
+    _COLL.clear()
+    for k in list(_AVERAGERS.keys()):
+        del _AVERAGERS[k]
+
+
+def num_processes() -> int:
+    return bootstrap.world().size
+
+
+def mpi_all_reduce(tensor: torch.Tensor, op: str = SUM) -> torch.Tensor:
+    """In-place all-reduce(SUM) of a tensor on this rank's device."""
+    if op != SUM:
+        raise ValueError("only SUM is supported (the reference only ever uses MPI.SUM)")
+    if num_processes() > 1:
+        import torch.distributed as dist
+        dist.all_reduce(tensor)
+    return tensor
+
+
+def mpi_sum(x: Any, op: str = SUM):
+    """Sum ``x`` (python scalar, numpy array or tensor) over all ranks; fp32 like the
+    reference (mpi_tools.py:19-27).  Scalars come back as python floats, arrays as numpy
+    float32 arrays, tensors as tensors."""
+    w = bootstrap.world()
+    is_tensor = torch.is_tensor(x)
+    scalar = (not is_tensor) and np.isscalar(x)
+    dev = w.device if w.backend == "nccl" else torch.device("cpu")
+    t = (x.detach().to(dev, torch.float32).clone() if is_tensor
+         else torch.as_tensor(np.asarray([x] if scalar else x, dtype=np.float32)).to(dev))
+    mpi_all_reduce(t, op)
+    if is_tensor:
+        return t.to(x.device)
+    out = t.cpu().numpy()
+    return float(out[0]) if scalar else out
+
+
+def mpi_broadcast(x: torch.Tensor, root: int = 0) -> torch.Tensor:
+    """Broadcast rank ``root``'s values into ``x`` in place (mpi_tools.py:40-44)."""
+    if num_processes() > 1:
+        import torch.distributed as dist
+        w = bootstrap.world()
+        if w.backend == "nccl" and not x.is_cuda:
+            tmp = x.to(w.device)
+            dist.broadcast(tmp, src=root)
+            x.copy_(tmp)
+        else:
+            dist.broadcast(x, src=root)
+    return x
+
+
+class _GradAverager:
+    def __init__(self, model: nn.Module, bucket_mb: float = 32.0):
+        self.coll = _collectives()
+        w = bootstrap.world()
+        params = [p for p in model.parameters() if p.requires_grad]
+        self.device = params[0].device if params else w.device
+        self.layout = FlatLayout(params, int(bucket_mb * 2 ** 20), w.size)
+        self.arena = alloc_arena(self.layout.total, torch.float32, self.device, self.coll.alloc)
+
+    @torch.no_grad()
+    def average(self) -> None:
+        src, dst, rebind = [], [], []
+        for p in self.layout.params:
+            v = self.layout.view(self.arena, p)
+            if p.grad is None:                       # unused this step: contributes zeros
+                v.zero_()
+                continue
+            if p.grad.data_ptr() != v.data_ptr() or p.grad.dtype != torch.float32:
+                src.append(p.grad)
+                dst.append(v)
+                rebind.append((p, v))
+        if src:
+            torch._foreach_copy_(dst, src)
+        for b in self.layout.buckets:
+            self.coll.all_reduce_avg_(self.layout.bucket_view(self.arena, b))
+        self.coll.sync_stream()
+        for p, v in rebind:
+            if p.grad.dtype == torch.float32:
+                p.grad = v                            # next step accumulates straight into the arena
+            else:
+                p.grad.copy_(v)
+
+
+def mpi_avg_grads(model: nn.Module) -> None:
+    """Average gradients across ranks (mpi_tools.py:30-37): no-op for one process."""
+    if num_processes() == 1:
+        return None
+    av = _AVERAGERS.get(model)
+    if av is None:
+        av = _AVERAGERS[model] = _GradAverager(model)
+    av.average()
+    return None
+
+
+@torch.no_grad()
+def sync_params(model: nn.Module, root: int = 0, include_buffers: bool = True) -> None:
+    """Make every rank hold rank-``root``'s weights (mpi_tools.py:47-53) -- as ONE flat
+    broadcast, and including buffers such as BN running statistics."""
+    if num_processes() == 1:
+        return None
+    coll = _collectives()
+    tensors = [p.data for p in model.parameters()]
+    if include_buffers:
+        tensors += [b for b in model.buffers()]
+    tensors = [t for t in tensors if t.numel() > 0]
+    if not tensors:
+        return None
+    dev = tensors[0].device
+    total = sum(t.numel() for t in tensors)
+    stage = coll.alloc(total, torch.float32)
+    if stage.device != dev:
+        stage = torch.zeros(total, dtype=torch.float32, device=dev)
+    off = 0
+    views = []
+    for t in tensors:
+        v = stage[off:off + t.numel()]
+        views.append(v)
+        off += t.numel()
+    for t, v in zip(tensors, views):
+        v.copy_(t.reshape(-1))                        # logical (row-major) order, cast to fp32
+    coll.broadcast_(stage, root)
+    coll.sync_stream()
+    for t, v in zip(tensors, views):
+        t.copy_(v.view(t.shape))
+    return None
