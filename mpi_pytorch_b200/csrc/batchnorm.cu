@@ -1,0 +1,248 @@
+// K7: BatchNorm (+ residual add) (+ ReLU), NHWC, training forward/backward and eval affine.
+// Replaces the ATen CPU batch_norm + relu + add the reference runs for every ResNet / VGG-bn /
+// DenseNet / Inception block.  x is [M = N*H*W, C] with C contiguous.
+//
+//  forward (train):  stats  : sums[0:C] = sum_m x, sums[C:2C] = sum_m x^2   (skipped when the conv
+//                             epilogue already produced them)
+//                    apply  : out = relu( (x-mean)*invstd*gamma + beta + residual ), saves mean/invstd,
+//                             updates running_mean / running_var (unbiased) like torch
+//  backward        : reduce : dsum[0:C] = sum dzm,  dsum[C:2C] = sum dzm * xhat,  dzm = dz * (out > 0)
+//                    apply  : dx = gamma*invstd*(dzm - dsum0/M - xhat*dsum1/M);  dres = dzm
+// Thread mapping: 8 channels per thread (16 B bf16 vectors), blockDim = cvecs * rows_per_block so a
+// thread keeps the same channel group for its whole row loop and can accumulate in registers.
+#include "common.cuh"
+
+using namespace mpb;
+
+namespace {
+
+struct Map {
+  int cvecs, rows_per_block, threads;
+};
+inline Map make_map(int C) {
+  Map m;
+  m.cvecs = C / 8;
+  m.rows_per_block = 256 / m.cvecs;
+  if (m.rows_per_block < 1) m.rows_per_block = 1;
+  m.threads = m.cvecs * m.rows_per_block;
+  return m;
+}
+inline int rows_grid(long long M, int rows_per_block, int waves) {
+  long long b = (M + rows_per_block - 1) / rows_per_block;
+  const long long cap = (long long)kSMs * waves;
+  return (int)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+// Reduce per-thread acc[8] x2 over the rows_per_block threads sharing a channel group, then atomics.
+__device__ __forceinline__ void reduce_pair_to_global(float (&a)[8], float (&b)[8], float* g0, float* g1, int cvecs,
+                                                      int rows_per_block, float* smem /* threads*16 floats */) {
+  const int t = threadIdx.x;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { smem[t * 16 + k] = a[k]; smem[t * 16 + 8 + k] = b[k]; }
+  __syncthreads();
+  // cvecs*16 output values; thread u handles value u (and strides) summing over rows_per_block partials
+  for (int u = t; u < cvecs * 16; u += blockDim.x) {
+    const int cv = u >> 4, k = u & 15;
+    float s = 0.f;
+    for (int r = 0; r < rows_per_block; ++r) s += smem[(r * cvecs + cv) * 16 + k];
+    if (k < 8) atomicAdd(g0 + cv * 8 + k, s);
+    else atomicAdd(g1 + cv * 8 + (k - 8), s);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, float* __restrict__ sums, long long M,
+                                                       int C, int cvecs, int rows_per_block) {
+  extern __shared__ float smem[];
+  const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
+  float s[8] = {0}, q[8] = {0};
+  for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += (long long)gridDim.x * rows_per_block) {
+    float v[8];
+    load8(x + m * C + cv * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] += v[k] * v[k]; }
+  }
+  reduce_pair_to_global(s, q, sums, sums + C, cvecs, rows_per_block, smem);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bn_fwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                                                           T* __restrict__ out, const float* __restrict__ sums,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           float* __restrict__ run_mean, float* __restrict__ run_var,
+                                                           float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                                                           long long M, int C, int cvecs, int rows_per_block, float eps,
+                                                           float momentum, int relu, int training) {
+  const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
+  float sc[8], sh[8];
+  const float invM = 1.f / (float)M;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cv * 8 + k;
+    float mean, var;
+    if (training) {
+      mean = sums[c] * invM;
+      var = fmaxf(sums[C + c] * invM - mean * mean, 0.f);
+    } else {
+      mean = run_mean[c];
+      var = run_var[c];
+    }
+    const float invstd = rsqrtf(var + eps);
+    const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+    sc[k] = g * invstd;
+    sh[k] = b - mean * sc[k];
+    if (training && blockIdx.x == 0 && r == 0) {
+      save_mean[c] = mean;
+      save_invstd[c] = invstd;
+      if (run_mean) {
+        const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+        run_mean[c] = (1.f - momentum) * run_mean[c] + momentum * mean;
+        run_var[c] = (1.f - momentum) * run_var[c] + momentum * unbiased;
+      }
+    }
+  }
+  for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += (long long)gridDim.x * rows_per_block) {
+    float v[8];
+    load8(x + m * C + cv * 8, v);
+    if (res) {
+      float rr[8];
+      load8(res + m * C + cv * 8, rr);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = fmaf(v[k], sc[k], sh[k]) + rr[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = fmaf(v[k], sc[k], sh[k]);
+    }
+    if (relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+    }
+    store8(out + m * C + cv * 8, v);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict__ dz, const T* __restrict__ z,
+                                                            const T* __restrict__ x, const float* __restrict__ save_mean,
+                                                            const float* __restrict__ save_invstd,
+                                                            float* __restrict__ dsum, long long M, int C, int cvecs,
+                                                            int rows_per_block, int relu) {
+  extern __shared__ float smem[];
+  const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
+  float mean[8], istd[8], s0[8] = {0}, s1[8] = {0};
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { mean[k] = save_mean[cv * 8 + k]; istd[k] = save_invstd[cv * 8 + k]; }
+  for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += (long long)gridDim.x * rows_per_block) {
+    float g[8], xv[8];
+    load8(dz + m * C + cv * 8, g);
+    load8(x + m * C + cv * 8, xv);
+    if (relu) {
+      float zv[8];
+      load8(z + m * C + cv * 8, zv);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = zv[k] > 0.f ? g[k] : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { s0[k] += g[k]; s1[k] += g[k] * (xv[k] - mean[k]) * istd[k]; }
+  }
+  reduce_pair_to_global(s0, s1, dsum, dsum + C, cvecs, rows_per_block, smem);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__ dz, const T* __restrict__ z,
+                                                           const T* __restrict__ x, const float* __restrict__ gamma,
+                                                           const float* __restrict__ save_mean,
+                                                           const float* __restrict__ save_invstd,
+                                                           const float* __restrict__ dsum, T* __restrict__ dx,
+                                                           T* __restrict__ dres, float* __restrict__ dgamma,
+                                                           float* __restrict__ dbeta, long long M, int C, int cvecs,
+                                                           int rows_per_block, int relu) {
+  const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
+  float mean[8], istd[8], a[8], b0[8], b1[8];
+  const float invM = 1.f / (float)M;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cv * 8 + k;
+    mean[k] = save_mean[c];
+    istd[k] = save_invstd[c];
+    const float g = gamma ? gamma[c] : 1.f;
+    a[k] = g * istd[k];
+    b0[k] = dsum[c] * invM;
+    b1[k] = dsum[C + c] * invM;
+    if (blockIdx.x == 0 && r == 0) {
+      if (dgamma) dgamma[c] = dsum[C + c];
+      if (dbeta) dbeta[c] = dsum[c];
+    }
+  }
+  for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += (long long)gridDim.x * rows_per_block) {
+    float g[8], xv[8];
+    load8(dz + m * C + cv * 8, g);
+    load8(x + m * C + cv * 8, xv);
+    if (relu) {
+      float zv[8];
+      load8(z + m * C + cv * 8, zv);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = zv[k] > 0.f ? g[k] : 0.f;
+    }
+    if (dres) store8(dres + m * C + cv * 8, g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float xhat = (xv[k] - mean[k]) * istd[k];
+      xv[k] = a[k] * (g[k] - b0[k] - xhat * b1[k]);
+    }
+    store8(dx + m * C + cv * 8, xv);
+  }
+}
+
+}  // namespace
+
+#define DISPATCH_T(dtype, ...)                               \
+  if (dtype == MPB_BF16) { using T = __nv_bfloat16; __VA_ARGS__ } \
+  else { using T = float; __VA_ARGS__ }
+
+// sums: 2*C floats, zeroed here.
+MPB_API int mpb_bn_stats(const void* x, float* sums, long long M, int C, int dtype, void* stream) {
+  if (C % 8 != 0 || C > 2048) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  MPB_CUDA(cudaMemsetAsync(sums, 0, 2 * C * sizeof(float), st));
+  const Map mp = make_map(C);
+  const int grid = rows_grid(M, mp.rows_per_block, 4);
+  const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
+  DISPATCH_T(dtype, bn_stats_kernel<T><<<grid, mp.threads, smem, st>>>((const T*)x, sums, M, C, mp.cvecs, mp.rows_per_block);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+
+MPB_API int mpb_bn_fwd_apply(const void* x, const void* res, void* out, const float* sums, const float* gamma,
+                             const float* beta, float* run_mean, float* run_var, float* save_mean, float* save_invstd,
+                             long long M, int C, float eps, float momentum, int relu, int training, int dtype,
+                             void* stream) {
+  if (C % 8 != 0 || C > 2048) return -1;
+  const Map mp = make_map(C);
+  const int grid = rows_grid(M, mp.rows_per_block, 8);
+  DISPATCH_T(dtype, bn_fwd_apply_kernel<T><<<grid, mp.threads, 0, (cudaStream_t)stream>>>(
+                        (const T*)x, (const T*)res, (T*)out, sums, gamma, beta, run_mean, run_var, save_mean,
+                        save_invstd, M, C, mp.cvecs, mp.rows_per_block, eps, momentum, relu, training);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+
+// dsum: 2*C floats scratch, zeroed here by the reduce call.
+MPB_API int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float* gamma, const float* save_mean,
+                       const float* save_invstd, float* dsum, void* dx, void* dres, float* dgamma, float* dbeta,
+                       long long M, int C, int relu, int dtype, void* stream) {
+  if (C % 8 != 0 || C > 2048) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));
+  const Map mp = make_map(C);
+  const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
+  const int g1 = rows_grid(M, mp.rows_per_block, 4), g2 = rows_grid(M, mp.rows_per_block, 8);
+  DISPATCH_T(dtype,
+             bn_bwd_reduce_kernel<T><<<g1, mp.threads, smem, st>>>((const T*)dz, (const T*)z, (const T*)x, save_mean,
+                                                                   save_invstd, dsum, M, C, mp.cvecs, mp.rows_per_block, relu);
+             bn_bwd_apply_kernel<T><<<g2, mp.threads, 0, st>>>((const T*)dz, (const T*)z, (const T*)x, gamma, save_mean,
+                                                               save_invstd, dsum, (T*)dx, (T*)dres, dgamma, dbeta, M, C,
+                                                               mp.cvecs, mp.rows_per_block, relu);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}

@@ -1,0 +1,317 @@
+// K8 pooling (NHWC): max (with uint8 window-argmax for an exact, atomic-free backward), average
+// (count_include_pad / ceil_mode), adaptive average -> any output size; plus K11 elementwise bits
+// (ReLU fwd/bwd, dropout with a stateless hash mask).  Replaces the ATen CPU pooling / relu / dropout
+// calls listed in SURVEY §2.5.  8 channels per thread, C contiguous.
+#include "common.cuh"
+
+using namespace mpb;
+
+namespace {
+
+struct PoolGeom {
+  int N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                          unsigned char* __restrict__ idx, PoolGeom g) {
+  const int cvecs = g.C / 8;
+  const long long total = (long long)g.N * g.Ho * g.Wo * cvecs;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % cvecs);
+    long long t = i / cvecs;
+    const int wo = (int)(t % g.Wo); t /= g.Wo;
+    const int ho = (int)(t % g.Ho);
+    const int n = (int)(t / g.Ho);
+    float best[8];
+    unsigned char bi[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { best[k] = -INFINITY; bi[k] = 0; }
+    bool first = true;
+    for (int r = 0; r < g.kh; ++r) {
+      const int h = ho * g.sh - g.ph + r;
+      if (h < 0 || h >= g.H) continue;
+      for (int s = 0; s < g.kw; ++s) {
+        const int w = wo * g.sw - g.pw + s;
+        if (w < 0 || w >= g.W) continue;
+        float v[8];
+        load8(x + (((long long)n * g.H + h) * g.W + w) * g.C + cv * 8, v);
+        const unsigned char pos = (unsigned char)(r * g.kw + s);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (first || v[k] > best[k] || v[k] != v[k]) { best[k] = v[k]; bi[k] = pos; }   // torch: first max, NaN wins
+        first = false;
+      }
+    }
+    const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
+    store8(y + o, best);
+    if (idx) *reinterpret_cast<uint2*>(idx + o) = *reinterpret_cast<uint2*>(bi);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ dy, const unsigned char* __restrict__ idx,
+                                                          T* __restrict__ dx, PoolGeom g) {
+  const int cvecs = g.C / 8;
+  const long long total = (long long)g.N * g.H * g.W * cvecs;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % cvecs);
+    long long t = i / cvecs;
+    const int w = (int)(t % g.W); t /= g.W;
+    const int h = (int)(t % g.H);
+    const int n = (int)(t / g.H);
+    float acc[8] = {0};
+    // output windows containing (h, w): ho*sh - ph <= h < ho*sh - ph + kh
+    int ho_lo = (h + g.ph - g.kh + g.sh) / g.sh; if (h + g.ph - g.kh + 1 <= 0) ho_lo = 0;
+    int wo_lo = (w + g.pw - g.kw + g.sw) / g.sw; if (w + g.pw - g.kw + 1 <= 0) wo_lo = 0;
+    const int ho_hi = min((h + g.ph) / g.sh, g.Ho - 1), wo_hi = min((w + g.pw) / g.sw, g.Wo - 1);
+    for (int ho = ho_lo; ho <= ho_hi; ++ho) {
+      const int r = h - (ho * g.sh - g.ph);
+      if (r < 0 || r >= g.kh) continue;
+      for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+        const int s = w - (wo * g.sw - g.pw);
+        if (s < 0 || s >= g.kw) continue;
+        const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
+        const uint2 packed = *reinterpret_cast<const uint2*>(idx + o);
+        const unsigned char* bi = reinterpret_cast<const unsigned char*>(&packed);
+        float gy[8];
+        load8(dy + o, gy);
+        const unsigned char pos = (unsigned char)(r * g.kw + s);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += (bi[k] == pos) ? gy[k] : 0.f;
+      }
+    }
+    store8(dx + i * 8, acc);
+  }
+}
+
+// avg pool; divisor semantics follow torch (count_include_pad with ceil_mode clipping).
+template <typename T, bool BWD>
+__global__ void __launch_bounds__(256) avgpool_kernel(const T* __restrict__ in, T* __restrict__ out, PoolGeom g,
+                                                      int count_include_pad) {
+  const int cvecs = g.C / 8;
+  if (!BWD) {
+    const long long total = (long long)g.N * g.Ho * g.Wo * cvecs;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+      const int cv = (int)(i % cvecs);
+      long long t = i / cvecs;
+      const int wo = (int)(t % g.Wo); t /= g.Wo;
+      const int ho = (int)(t % g.Ho);
+      const int n = (int)(t / g.Ho);
+      int h0 = ho * g.sh - g.ph, w0 = wo * g.sw - g.pw;
+      int h1 = min(h0 + g.kh, g.H + g.ph), w1 = min(w0 + g.kw, g.W + g.pw);
+      const int pool = (h1 - h0) * (w1 - w0);
+      h0 = max(h0, 0); w0 = max(w0, 0); h1 = min(h1, g.H); w1 = min(w1, g.W);
+      const float div = (float)(count_include_pad ? pool : (h1 - h0) * (w1 - w0));
+      float acc[8] = {0};
+      for (int h = h0; h < h1; ++h)
+        for (int w = w0; w < w1; ++w) {
+          float v[8];
+          load8(in + (((long long)n * g.H + h) * g.W + w) * g.C + cv * 8, v);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += v[k];
+        }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] /= div;
+      store8(out + i * 8, acc);
+    }
+  } else {  // in = dy [N,Ho,Wo,C], out = dx [N,H,W,C]
+    const long long total = (long long)g.N * g.H * g.W * cvecs;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+      const int cv = (int)(i % cvecs);
+      long long t = i / cvecs;
+      const int w = (int)(t % g.W); t /= g.W;
+      const int h = (int)(t % g.H);
+      const int n = (int)(t / g.H);
+      float acc[8] = {0};
+      int ho_lo = (h + g.ph - g.kh + g.sh) / g.sh; if (h + g.ph - g.kh + 1 <= 0) ho_lo = 0;
+      int wo_lo = (w + g.pw - g.kw + g.sw) / g.sw; if (w + g.pw - g.kw + 1 <= 0) wo_lo = 0;
+      const int ho_hi = min((h + g.ph) / g.sh, g.Ho - 1), wo_hi = min((w + g.pw) / g.sw, g.Wo - 1);
+      for (int ho = ho_lo; ho <= ho_hi; ++ho) {
+        int h0 = ho * g.sh - g.ph;
+        if (h < h0 || h >= h0 + g.kh) continue;
+        for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+          int w0 = wo * g.sw - g.pw;
+          if (w < w0 || w >= w0 + g.kw) continue;
+          int hh0 = h0, ww0 = w0;
+          int h1 = min(hh0 + g.kh, g.H + g.ph), w1 = min(ww0 + g.kw, g.W + g.pw);
+          const int pool = (h1 - hh0) * (w1 - ww0);
+          hh0 = max(hh0, 0); ww0 = max(ww0, 0); h1 = min(h1, g.H); w1 = min(w1, g.W);
+          const float div = (float)(count_include_pad ? pool : (h1 - hh0) * (w1 - ww0));
+          float gy[8];
+          load8(in + (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8, gy);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += gy[k] / div;
+        }
+      }
+      store8(out + i * 8, acc);
+    }
+  }
+}
+
+__device__ __forceinline__ int ada_start(int o, int in, int out) { return (int)(((long long)o * in) / out); }
+__device__ __forceinline__ int ada_end(int o, int in, int out) { return (int)((((long long)(o + 1)) * in + out - 1) / out); }
+
+template <typename T, bool BWD>
+__global__ void __launch_bounds__(256) adaptive_avg_kernel(const T* __restrict__ in, T* __restrict__ out, PoolGeom g) {
+  const int cvecs = g.C / 8;
+  if (!BWD) {
+    const long long total = (long long)g.N * g.Ho * g.Wo * cvecs;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+      const int cv = (int)(i % cvecs);
+      long long t = i / cvecs;
+      const int wo = (int)(t % g.Wo); t /= g.Wo;
+      const int ho = (int)(t % g.Ho);
+      const int n = (int)(t / g.Ho);
+      const int h0 = ada_start(ho, g.H, g.Ho), h1 = ada_end(ho, g.H, g.Ho);
+      const int w0 = ada_start(wo, g.W, g.Wo), w1 = ada_end(wo, g.W, g.Wo);
+      float acc[8] = {0};
+      for (int h = h0; h < h1; ++h)
+        for (int w = w0; w < w1; ++w) {
+          float v[8];
+          load8(in + (((long long)n * g.H + h) * g.W + w) * g.C + cv * 8, v);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += v[k];
+        }
+      const float inv = 1.f / (float)((h1 - h0) * (w1 - w0));
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] *= inv;
+      store8(out + i * 8, acc);
+    }
+  } else {
+    const long long total = (long long)g.N * g.H * g.W * cvecs;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+      const int cv = (int)(i % cvecs);
+      long long t = i / cvecs;
+      const int w = (int)(t % g.W); t /= g.W;
+      const int h = (int)(t % g.H);
+      const int n = (int)(t / g.H);
+      float acc[8] = {0};
+      for (int ho = 0; ho < g.Ho; ++ho) {
+        const int h0 = ada_start(ho, g.H, g.Ho), h1 = ada_end(ho, g.H, g.Ho);
+        if (h < h0 || h >= h1) continue;
+        for (int wo = 0; wo < g.Wo; ++wo) {
+          const int w0 = ada_start(wo, g.W, g.Wo), w1 = ada_end(wo, g.W, g.Wo);
+          if (w < w0 || w >= w1) continue;
+          float gy[8];
+          load8(in + (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8, gy);
+          const float inv = 1.f / (float)((h1 - h0) * (w1 - w0));
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += gy[k] * inv;
+        }
+      }
+      store8(out + i * 8, acc);
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) relu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, long long n8) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float v[8];
+    load8(x + i * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+    store8(y + i * 8, v);
+  }
+}
+template <typename T>
+__global__ void __launch_bounds__(256) relu_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y,
+                                                       T* __restrict__ dx, long long n8) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float g[8], v[8];
+    load8(dy + i * 8, g);
+    load8(y + i * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = v[k] > 0.f ? g[k] : 0.f;
+    store8(dx + i * 8, g);
+  }
+}
+// y = x * keep/(1-p) with keep = hash(seed, i) >= p*2^32 ; the same call with the same seed on dy is the backward.
+template <typename T>
+__global__ void __launch_bounds__(256) dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long long n8,
+                                                      uint32_t seed, uint32_t thresh, float scale) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float v[8];
+    load8(x + i * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint32_t h = hash32((uint32_t)(i * 8 + k) ^ seed) ^ hash32((uint32_t)((i * 8 + k) >> 32) + seed * 0x9E3779B9u);
+      v[k] = (h >= thresh) ? v[k] * scale : 0.f;
+    }
+    store8(y + i * 8, v);
+  }
+}
+
+}  // namespace
+
+#define DISPATCH_T(dtype, ...)                               \
+  if (dtype == MPB_BF16) { using T = __nv_bfloat16; __VA_ARGS__ } \
+  else { using T = float; __VA_ARGS__ }
+
+static PoolGeom geom(int N, int H, int W, int C, int Ho, int Wo, int kh, int kw, int sh, int sw, int ph, int pw) {
+  PoolGeom g; g.N = N; g.H = H; g.W = W; g.C = C; g.Ho = Ho; g.Wo = Wo; g.kh = kh; g.kw = kw; g.sh = sh; g.sw = sw; g.ph = ph; g.pw = pw;
+  return g;
+}
+
+MPB_API int mpb_maxpool_fwd(const void* x, void* y, unsigned char* idx, int N, int H, int W, int C, int Ho, int Wo,
+                            int kh, int kw, int sh, int sw, int ph, int pw, int dtype, void* stream) {
+  if (C % 8 != 0 || kh * kw > 255) return -1;
+  const PoolGeom g = geom(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw);
+  const long long total = (long long)N * Ho * Wo * (C / 8);
+  DISPATCH_T(dtype, maxpool_fwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, g);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+MPB_API int mpb_maxpool_bwd(const void* dy, const unsigned char* idx, void* dx, int N, int H, int W, int C, int Ho,
+                            int Wo, int kh, int kw, int sh, int sw, int ph, int pw, int dtype, void* stream) {
+  if (C % 8 != 0) return -1;
+  const PoolGeom g = geom(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw);
+  const long long total = (long long)N * H * W * (C / 8);
+  DISPATCH_T(dtype, maxpool_bwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)dy, idx, (T*)dx, g);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+MPB_API int mpb_avgpool(const void* in, void* out, int N, int H, int W, int C, int Ho, int Wo, int kh, int kw, int sh,
+                        int sw, int ph, int pw, int count_include_pad, int backward, int dtype, void* stream) {
+  if (C % 8 != 0) return -1;
+  const PoolGeom g = geom(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw);
+  const long long total = (long long)N * (backward ? (long long)H * W : (long long)Ho * Wo) * (C / 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  DISPATCH_T(dtype, if (backward) avgpool_kernel<T, true><<<grid_for(total, 256), 256, 0, st>>>((const T*)in, (T*)out, g, count_include_pad);
+             else avgpool_kernel<T, false><<<grid_for(total, 256), 256, 0, st>>>((const T*)in, (T*)out, g, count_include_pad);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+MPB_API int mpb_adaptive_avgpool(const void* in, void* out, int N, int H, int W, int C, int Ho, int Wo, int backward,
+                                 int dtype, void* stream) {
+  if (C % 8 != 0) return -1;
+  const PoolGeom g = geom(N, H, W, C, Ho, Wo, 0, 0, 0, 0, 0, 0);
+  const long long total = (long long)N * (backward ? (long long)H * W : (long long)Ho * Wo) * (C / 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  DISPATCH_T(dtype, if (backward) adaptive_avg_kernel<T, true><<<grid_for(total, 256), 256, 0, st>>>((const T*)in, (T*)out, g);
+             else adaptive_avg_kernel<T, false><<<grid_for(total, 256), 256, 0, st>>>((const T*)in, (T*)out, g);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+MPB_API int mpb_relu_fwd(const void* x, void* y, long long n, int dtype, void* stream) {
+  if (n % 8 != 0) return -1;
+  DISPATCH_T(dtype, relu_fwd_kernel<T><<<grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, n / 8);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+MPB_API int mpb_relu_bwd(const void* dy, const void* y, void* dx, long long n, int dtype, void* stream) {
+  if (n % 8 != 0) return -1;
+  DISPATCH_T(dtype, relu_bwd_kernel<T><<<grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const T*)dy, (const T*)y, (T*)dx, n / 8);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+MPB_API int mpb_dropout(const void* x, void* y, long long n, unsigned int seed, float p, int dtype, void* stream) {
+  if (n % 8 != 0) return -1;
+  const double t = (double)p * 4294967296.0;
+  const uint32_t thresh = t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)t;
+  const float scale = p < 1.f ? 1.f / (1.f - p) : 0.f;
+  DISPATCH_T(dtype, dropout_kernel<T><<<grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, n / 8, seed, thresh, scale);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}

@@ -1,0 +1,511 @@
+"""CUDA execution path: ctypes bindings to ``libmpb200.so`` + autograd Functions.
+
+Layout contract: 4-D activations are channels-last (physical NHWC), dtype bf16 (fp32 is supported
+by every kernel too and is what the numerics tests use as "fp32 mode").  Parameters are fp32 masters;
+when the DP engine attached a bf16 shadow (``p._mpb_shadow``, refreshed by the fused all-reduce+Adam
+kernel) the compute kernels read that instead of casting.
+
+Importing this module on a machine without the built library raises: there is no silent fallback
+(the driver checks that the in-tree ``.so`` was really loaded by the GPU tests).
+"""
+from __future__ import annotations
+
+import ctypes
+import itertools
+import os
+from typing import Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+
+from ..build import lib_path
+
+_LIB = ctypes.CDLL(lib_path())
+LAUNCHES = {"n": 0}            # kernels launched through this module (bench.py's gpu_launches)
+FALLBACKS = {}                 # op -> count of calls that went to a library kernel (cuDNN/cuBLAS)
+
+c_void_p, c_int, c_ll, c_float = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return 1
+    if t.dtype == torch.float32:
+        return 0
+    raise TypeError("mpb kernels take fp32 or bf16, got {}".format(t.dtype))
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]):
+    return c_void_p(0 if t is None else t.data_ptr())
+
+
+def _check(rc: int, name: str) -> None:
+    if rc != 0:
+        raise RuntimeError("{} failed with code {}".format(name, rc))
+
+
+def _call(name: str, *args, launches: int = 1) -> None:
+    rc = getattr(_LIB, name)(*args)
+    LAUNCHES["n"] += launches
+    _check(rc, name)
+
+
+def _note_fallback(op: str) -> None:
+    FALLBACKS[op] = FALLBACKS.get(op, 0) + 1
+
+
+def _nhwc(x: torch.Tensor) -> torch.Tensor:
+    if x.dim() == 4 and not x.is_contiguous(memory_format=torch.channels_last):
+        return x.contiguous(memory_format=torch.channels_last)
+    return x
+
+
+def _pair(v) -> Tuple[int, int]:
+    return (int(v[0]), int(v[1])) if isinstance(v, (tuple, list)) else (int(v), int(v))
+
+
+def _compute_weight(w: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    sh = getattr(w, "_mpb_shadow", None)
+    if sh is not None and sh.dtype == dtype:
+        return sh
+    return w.detach().to(dtype) if w.dtype != dtype else w.detach()
+
+
+# =============================================================================== convolution / linear
+def _gemm():
+    from . import tc
+    return tc
+
+
+class _ConvFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, padding, dilation, groups, want_stats):
+        x = _nhwc(x)
+        w = _compute_weight(weight, x.dtype)
+        ctx.save_for_backward(x, w)
+        ctx.conf = (stride, padding, dilation, groups, bias is not None, weight.dtype)
+        tc = _gemm()
+        stats = None
+        if tc.conv_supported(x, w, stride, padding, dilation, groups):
+            y, stats = tc.conv_fprop(x, w, None if bias is None else bias.detach(), stride, padding, want_stats)
+        else:
+            _note_fallback("conv_fprop")
+            b = None if bias is None else bias.detach().to(x.dtype)
+            y = F.conv2d(x, w, b, stride, padding, dilation, groups)
+            y = _nhwc(y)
+        ctx.mark_non_differentiable(*([stats] if stats is not None else []))
+        if want_stats:
+            return y, stats
+        return y
+
+    @staticmethod
+    def backward(ctx, gy, *unused):
+        x, w = ctx.saved_tensors
+        stride, padding, dilation, groups, has_bias, wdtype = ctx.conf
+        gy = _nhwc(gy)
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        tc = _gemm()
+        gx = gw = gb = None
+        if tc.conv_supported(x, w, stride, padding, dilation, groups):
+            if need_x:
+                gx = tc.conv_dgrad(gy, w, x.shape, stride, padding)
+            if need_w:
+                gw = tc.conv_wgrad(gy, x, w.shape, stride, padding).to(wdtype)
+        else:
+            _note_fallback("conv_bwd")
+            gx, gw, _ = torch.ops.aten.convolution_backward(
+                gy, x, w, None, list(stride), list(padding), list(dilation), False, [0, 0], groups,
+                [need_x, need_w, False])
+            if gw is not None:
+                gw = gw.to(wdtype)
+        if has_bias and ctx.needs_input_grad[2]:
+            gb = gy.float().sum(dim=(0, 2, 3))
+        return gx, gw, gb, None, None, None, None, None
+
+
+def conv2d(x, w, b, stride, padding, dilation=(1, 1), groups=1):
+    if x.dtype not in (torch.bfloat16, torch.float32):
+        return F.conv2d(x, w, b, stride, padding, dilation, groups)
+    return _ConvFn.apply(x, w, b, _pair(stride), _pair(padding), _pair(dilation), int(groups), False)
+
+
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        w = _compute_weight(weight, x.dtype)
+        ctx.save_for_backward(x, w)
+        ctx.conf = (bias is not None, weight.dtype)
+        tc = _gemm()
+        if tc.gemm_supported(x, w):
+            return tc.linear_fwd(x, w, None if bias is None else bias.detach())
+        _note_fallback("linear_fwd")
+        return F.linear(x, w, None if bias is None else bias.detach().to(x.dtype))
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        has_bias, wdtype = ctx.conf
+        gy = gy.contiguous()
+        tc = _gemm()
+        gx = gw = gb = None
+        if tc.gemm_supported(x, w):
+            if ctx.needs_input_grad[0]:
+                gx = tc.linear_dx(gy, w)
+            if ctx.needs_input_grad[1]:
+                gw = tc.linear_dw(gy, x).to(wdtype)
+        else:
+            _note_fallback("linear_bwd")
+            if ctx.needs_input_grad[0]:
+                gx = gy @ w
+            if ctx.needs_input_grad[1]:
+                gw = (gy.t() @ x).to(wdtype)
+        if has_bias and ctx.needs_input_grad[2]:
+            gb = gy.float().sum(dim=0)
+        return gx, gw, gb
+
+
+def linear(x, w, b):
+    if x.dtype not in (torch.bfloat16, torch.float32) or x.dim() != 2:
+        return F.linear(x, w.to(x.dtype), None if b is None else b.to(x.dtype))
+    return _LinearFn.apply(x.contiguous(), w, b)
+
+
+# =============================================================================== batch norm (+add +relu)
+class _BNActFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, run_mean, run_var, eps, momentum, relu, training, sums):
+        x = _nhwc(x)
+        n, c, h, w = x.shape
+        m = n * h * w
+        res = _nhwc(residual) if residual is not None else None
+        out = torch.empty_like(x)
+        dev = x.device
+        save_mean = torch.empty(c, dtype=torch.float32, device=dev)
+        save_invstd = torch.empty(c, dtype=torch.float32, device=dev)
+        if training and sums is None:
+            sums = torch.empty(2 * c, dtype=torch.float32, device=dev)
+            _call("mpb_bn_stats", _p(x), _p(sums), c_ll(m), c_int(c), c_int(_dt(x)), c_void_p(_stream()), launches=2)
+        _call("mpb_bn_fwd_apply", _p(x), _p(res), _p(out), _p(sums), _p(gamma), _p(beta), _p(run_mean), _p(run_var),
+              _p(save_mean), _p(save_invstd), c_ll(m), c_int(c), c_float(eps), c_float(momentum), c_int(int(relu)),
+              c_int(int(training)), c_int(_dt(x)), c_void_p(_stream()))
+        ctx.save_for_backward(x, out, gamma, save_mean, save_invstd)
+        ctx.conf = (relu, residual is not None, training, c, m)
+        return out
+
+    @staticmethod
+    def backward(ctx, gz):
+        x, out, gamma, save_mean, save_invstd = ctx.saved_tensors
+        relu, has_res, training, c, m = ctx.conf
+        if not training:
+            raise RuntimeError("backward through eval-mode BatchNorm is not supported on the native path")
+        gz = _nhwc(gz)
+        if gz.dtype != x.dtype:
+            gz = gz.to(x.dtype)
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if has_res else None
+        dsum = torch.empty(2 * c, dtype=torch.float32, device=x.device)
+        dgamma = torch.empty(c, dtype=torch.float32, device=x.device)
+        dbeta = torch.empty(c, dtype=torch.float32, device=x.device)
+        _call("mpb_bn_bwd", _p(gz), _p(out), _p(x), _p(gamma), _p(save_mean), _p(save_invstd), _p(dsum), _p(dx), _p(dres),
+              _p(dgamma), _p(dbeta), c_ll(m), c_int(c), c_int(int(relu)), c_int(_dt(x)), c_void_p(_stream()), launches=3)
+        if has_res and not relu:
+            dres = gz
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None
+
+
+def _bn_ok(x, bn) -> bool:
+    c = x.shape[1]
+    return (x.dim() == 4 and c % 8 == 0 and c <= 2048 and x.dtype in (torch.bfloat16, torch.float32)
+            and bn.affine and bn.track_running_stats)
+
+
+def batch_norm_act(x, bn, residual=None, relu=False, sums=None):
+    if not _bn_ok(x, bn) or (not bn.training and torch.is_grad_enabled() and x.requires_grad):
+        from . import reference as ref
+        _note_fallback("batch_norm")
+        return ref.batch_norm_act(x, bn, residual, relu)
+    momentum = 0.1 if bn.momentum is None else float(bn.momentum)
+    if bn.training:
+        bn.num_batches_tracked.add_(1)
+    return _BNActFn.apply(x, bn.weight, bn.bias, residual, bn.running_mean, bn.running_var, float(bn.eps), momentum,
+                          bool(relu), bool(bn.training), sums)
+
+
+def conv_bn_act(x, conv, bn, relu=True, residual=None):
+    if x.dtype not in (torch.bfloat16, torch.float32):
+        x = x.to(torch.bfloat16)
+    want_stats = bn.training and _bn_ok_channels(conv.out_channels)
+    res = _ConvFn.apply(x, conv.weight, conv.bias, _pair(conv.stride), _pair(conv.padding), _pair(conv.dilation),
+                        int(conv.groups), want_stats)
+    y, sums = res if want_stats else (res, None)
+    return batch_norm_act(y, bn, residual, relu, sums)
+
+
+def _bn_ok_channels(c: int) -> bool:
+    return c % 8 == 0 and c <= 2048
+
+
+# =============================================================================== elementwise
+class _ReluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y = torch.empty_like(x)
+        _call("mpb_relu_fwd", _p(x), _p(y), c_ll(x.numel()), c_int(_dt(x)), c_void_p(_stream()))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        (y,) = ctx.saved_tensors
+        gy = gy.contiguous(memory_format=torch.channels_last) if (y.dim() == 4 and y.is_contiguous(
+            memory_format=torch.channels_last)) else gy.contiguous()
+        dx = torch.empty_like(y)
+        _call("mpb_relu_bwd", _p(gy), _p(y), _p(dx), c_ll(y.numel()), c_int(_dt(y)), c_void_p(_stream()))
+        return dx
+
+
+def _dense(x: torch.Tensor) -> bool:
+    return x.is_contiguous() or (x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last))
+
+
+def relu(x, inplace=False):
+    if x.numel() % 8 != 0 or x.dtype not in (torch.bfloat16, torch.float32) or not _dense(x):
+        return F.relu(x, inplace=inplace)
+    return _ReluFn.apply(x)
+
+
+_DROP_SEED = itertools.count(0x5EED)
+
+
+class _DropoutFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p, seed):
+        y = torch.empty_like(x)
+        _call("mpb_dropout", _p(x), _p(y), c_ll(x.numel()), ctypes.c_uint(seed), c_float(p), c_int(_dt(x)),
+              c_void_p(_stream()))
+        ctx.conf = (p, seed)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        p, seed = ctx.conf
+        gy = gy.contiguous()
+        dx = torch.empty_like(gy)
+        _call("mpb_dropout", _p(gy), _p(dx), c_ll(gy.numel()), ctypes.c_uint(seed), c_float(p), c_int(_dt(gy)),
+              c_void_p(_stream()))
+        return dx, None, None
+
+
+def dropout(x, p):
+    if x.numel() % 8 != 0 or x.dtype not in (torch.bfloat16, torch.float32) or not x.is_contiguous():
+        return F.dropout(x, p, True)
+    return _DropoutFn.apply(x, float(p), next(_DROP_SEED) & 0xFFFFFFFF)
+
+
+# =============================================================================== pooling
+def _out_size(i: int, k: int, s: int, p: int, ceil_mode: bool) -> int:
+    if ceil_mode:
+        o = -(-(i + 2 * p - k) // s) + 1
+        if (o - 1) * s >= i + p:
+            o -= 1
+    else:
+        o = (i + 2 * p - k) // s + 1
+    return o
+
+
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, s, p, ceil_mode):
+        x = _nhwc(x)
+        n, c, h, w = x.shape
+        ho, wo = _out_size(h, k[0], s[0], p[0], ceil_mode), _out_size(w, k[1], s[1], p[1], ceil_mode)
+        y = torch.empty((n, c, ho, wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+        idx = torch.empty((n, ho, wo, c), dtype=torch.uint8, device=x.device)
+        _call("mpb_maxpool_fwd", _p(x), _p(y), _p(idx), c_int(n), c_int(h), c_int(w), c_int(c), c_int(ho), c_int(wo),
+              c_int(k[0]), c_int(k[1]), c_int(s[0]), c_int(s[1]), c_int(p[0]), c_int(p[1]), c_int(_dt(x)),
+              c_void_p(_stream()))
+        ctx.save_for_backward(idx)
+        ctx.conf = (x.shape, k, s, p)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        (idx,) = ctx.saved_tensors
+        shape, k, s, p = ctx.conf
+        n, c, h, w = shape
+        gy = _nhwc(gy)
+        ho, wo = gy.shape[2], gy.shape[3]
+        dx = torch.empty(shape, dtype=gy.dtype, device=gy.device, memory_format=torch.channels_last)
+        _call("mpb_maxpool_bwd", _p(gy), _p(idx), _p(dx), c_int(n), c_int(h), c_int(w), c_int(c), c_int(ho), c_int(wo),
+              c_int(k[0]), c_int(k[1]), c_int(s[0]), c_int(s[1]), c_int(p[0]), c_int(p[1]), c_int(_dt(gy)),
+              c_void_p(_stream()))
+        return dx, None, None, None, None
+
+
+def max_pool2d(x, k, s, p, ceil_mode=False):
+    k, s, p = _pair(k), _pair(s), _pair(p)
+    if x.dim() != 4 or x.shape[1] % 8 != 0 or x.dtype not in (torch.bfloat16, torch.float32):
+        _note_fallback("max_pool2d")
+        return F.max_pool2d(x, k, s, p, 1, ceil_mode)
+    return _MaxPoolFn.apply(x, k, s, p, bool(ceil_mode))
+
+
+class _AvgPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, s, p, ceil_mode, cip):
+        x = _nhwc(x)
+        n, c, h, w = x.shape
+        ho, wo = _out_size(h, k[0], s[0], p[0], ceil_mode), _out_size(w, k[1], s[1], p[1], ceil_mode)
+        y = torch.empty((n, c, ho, wo), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+        _call("mpb_avgpool", _p(x), _p(y), c_int(n), c_int(h), c_int(w), c_int(c), c_int(ho), c_int(wo), c_int(k[0]),
+              c_int(k[1]), c_int(s[0]), c_int(s[1]), c_int(p[0]), c_int(p[1]), c_int(int(cip)), c_int(0), c_int(_dt(x)),
+              c_void_p(_stream()))
+        ctx.conf = (x.shape, k, s, p, cip)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        shape, k, s, p, cip = ctx.conf
+        n, c, h, w = shape
+        gy = _nhwc(gy)
+        dx = torch.empty(shape, dtype=gy.dtype, device=gy.device, memory_format=torch.channels_last)
+        _call("mpb_avgpool", _p(gy), _p(dx), c_int(n), c_int(h), c_int(w), c_int(c), c_int(gy.shape[2]),
+              c_int(gy.shape[3]), c_int(k[0]), c_int(k[1]), c_int(s[0]), c_int(s[1]), c_int(p[0]), c_int(p[1]),
+              c_int(int(cip)), c_int(1), c_int(_dt(gy)), c_void_p(_stream()))
+        return dx, None, None, None, None, None
+
+
+def avg_pool2d(x, k, s, p, ceil_mode=False, count_include_pad=True):
+    k, s, p = _pair(k), _pair(s), _pair(p)
+    if x.dim() != 4 or x.shape[1] % 8 != 0 or x.dtype not in (torch.bfloat16, torch.float32):
+        _note_fallback("avg_pool2d")
+        return F.avg_pool2d(x, k, s, p, ceil_mode, count_include_pad)
+    return _AvgPoolFn.apply(x, k, s, p, bool(ceil_mode), bool(count_include_pad))
+
+
+class _AdaptiveAvgFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, out_hw):
+        x = _nhwc(x)
+        n, c, h, w = x.shape
+        y = torch.empty((n, c, out_hw[0], out_hw[1]), dtype=x.dtype, device=x.device,
+                        memory_format=torch.channels_last)
+        _call("mpb_adaptive_avgpool", _p(x), _p(y), c_int(n), c_int(h), c_int(w), c_int(c), c_int(out_hw[0]),
+              c_int(out_hw[1]), c_int(0), c_int(_dt(x)), c_void_p(_stream()))
+        ctx.conf = (x.shape, out_hw)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        shape, out_hw = ctx.conf
+        n, c, h, w = shape
+        gy = _nhwc(gy)
+        dx = torch.empty(shape, dtype=gy.dtype, device=gy.device, memory_format=torch.channels_last)
+        _call("mpb_adaptive_avgpool", _p(gy), _p(dx), c_int(n), c_int(h), c_int(w), c_int(c), c_int(out_hw[0]),
+              c_int(out_hw[1]), c_int(1), c_int(_dt(gy)), c_void_p(_stream()))
+        return dx, None
+
+
+def adaptive_avg_pool2d(x, out):
+    out = _pair(out)
+    if x.dim() != 4 or x.shape[1] % 8 != 0 or x.dtype not in (torch.bfloat16, torch.float32):
+        _note_fallback("adaptive_avg_pool2d")
+        return F.adaptive_avg_pool2d(x, out)
+    return _AdaptiveAvgFn.apply(x, out)
+
+
+# =============================================================================== loss / metrics
+class _CrossEntropyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        logits = logits.contiguous()
+        b, c = logits.shape
+        dl = torch.empty_like(logits)
+        loss = torch.empty((), dtype=torch.float32, device=logits.device)
+        _call("mpb_softmax_ce", _p(logits), _p(target), _p(dl), _p(loss), c_void_p(0), c_int(b), c_int(c),
+              c_int(_dt(logits)), c_void_p(_stream()), launches=2)
+        ctx.save_for_backward(dl)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return dl * g.to(dl.dtype), None
+
+
+def cross_entropy(logits, target):
+    if logits.dim() != 2 or logits.dtype not in (torch.bfloat16, torch.float32):
+        return F.cross_entropy(logits.float(), target)
+    return _CrossEntropyFn.apply(logits, target.contiguous())
+
+
+def count_correct(logits, target):
+    logits = logits.contiguous()
+    if logits.dtype not in (torch.bfloat16, torch.float32):
+        logits = logits.float()
+    out = torch.empty((), dtype=torch.int64, device=logits.device)
+    _call("mpb_count_correct", _p(logits), _p(target.contiguous()), _p(out), c_int(logits.shape[0]),
+          c_int(logits.shape[1]), c_int(_dt(logits)), c_void_p(_stream()), launches=2)
+    return out
+
+
+# =============================================================================== optimizer (local half of K1)
+def adam_flat(p, g, m, v, shadow, step, lr, b1, b2, eps, wd, grad_scale=1.0):
+    _call("mpb_adam_flat", _p(p), _p(g), _p(m), _p(v), _p(shadow), c_ll(p.numel()), c_int(step), c_float(lr), c_float(b1),
+          c_float(b2), c_float(eps), c_float(wd), c_float(grad_scale), c_void_p(_stream()))
+
+
+def sgd_flat(p, g, buf, shadow, step, lr, momentum, wd, grad_scale=1.0):
+    _call("mpb_sgd_flat", _p(p), _p(g), _p(buf), _p(shadow), c_ll(p.numel()), c_int(step), c_float(lr), c_float(momentum),
+          c_float(wd), c_float(grad_scale), c_void_p(_stream()))
+
+
+def cast_f32_bf16(src, dst):
+    _call("mpb_cast_f32_bf16", _p(src), _p(dst), c_ll(src.numel()), c_void_p(_stream()))
+
+
+# =============================================================================== preprocessing / data
+def resize_normalize(img_u8, out_h, out_w, mode="bilinear", dtype=torch.float32, channels_last=False):
+    single = img_u8.dim() == 3
+    x = (img_u8.unsqueeze(0) if single else img_u8).contiguous()
+    n, hi, wi, _ = x.shape
+    if channels_last:
+        out = torch.empty((n, 3, out_h, out_w), dtype=dtype, device=x.device, memory_format=torch.channels_last)
+    else:
+        out = torch.empty((n, 3, out_h, out_w), dtype=dtype, device=x.device)
+    kmode = 2 if mode == "bilinear" else 1
+    _call("mpb_resize", _p(x), _p(out), c_int(n), c_int(hi), c_int(wi), c_int(out_h), c_int(out_w),
+          c_int(int(mode == "bicubic")), c_int(kmode), c_int(int(channels_last)), c_int(_dt(out)), c_void_p(_stream()))
+    return out[0] if single else out
+
+
+def resize_u8(img_u8_nhwc, out_h, out_w, mode="bicubic"):
+    x = img_u8_nhwc.contiguous()
+    n, hi, wi, _ = x.shape
+    out = torch.empty((n, out_h, out_w, 3), dtype=torch.uint8, device=x.device)
+    _call("mpb_resize", _p(x), _p(out), c_int(n), c_int(hi), c_int(wi), c_int(out_h), c_int(out_w),
+          c_int(int(mode == "bicubic")), c_int(0), c_int(1), c_int(0), c_void_p(_stream()))
+    return out
+
+
+def normalize_u8(img_u8_nhwc, dtype=torch.float32):
+    x = img_u8_nhwc.contiguous()
+    n, h, w, _ = x.shape
+    out = torch.empty((n, 3, h, w), dtype=dtype, device=x.device)
+    _call("mpb_normalize_u8", _p(x), _p(out), c_int(n), c_int(h), c_int(w), c_int(0), c_int(_dt(out)), c_void_p(_stream()))
+    return out
+
+
+def synth_batch(seed, index, c, h, w, dtype, channels_last):
+    n = index.numel()
+    if channels_last:
+        out = torch.empty((n, c, h, w), dtype=dtype, device=index.device, memory_format=torch.channels_last)
+    else:
+        out = torch.empty((n, c, h, w), dtype=dtype, device=index.device)
+    _call("mpb_synth_images", _p(out), _p(index.contiguous()), c_int(n), c_int(c), c_int(h), c_int(w), c_ll(int(seed)),
+          c_int(int(channels_last)), c_int(_dt(out)), c_void_p(_stream()))
+    return out

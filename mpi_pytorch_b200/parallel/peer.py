@@ -1,0 +1,227 @@
+"""Peer-memory collectives: the host runtime around ``csrc/allreduce.cu``.
+
+One process per GPU.  Every arena handed out by :meth:`PeerCollectives.alloc` is a plain
+``cudaMalloc`` allocation whose ``cudaIpcMemHandle`` is exchanged through the bootstrap
+channel (``torch.distributed`` object all-gather -- plumbing only) and opened by every
+peer, so each rank ends up with a table ``ptrs[rank] -> device pointer`` for every
+symmetric buffer.  A view of such an arena is turned into "the same range on every rank"
+by adding its byte offset to each table entry.  The kernels then load / store through
+those pointers over NVLink 5 / NVSwitch and synchronise with system-scope release /
+acquire flags in a symmetric signal pad (no NCCL on this path).
+
+Algorithm choice per bucket (``auto``): one-shot up to ``ONESHOT_MAX_BYTES`` (latency
+bound: one barrier pair, every rank reduces everything), two-shot above (bandwidth
+bound: reduce-scatter by loads + all-gather by stores, optimizer state sliced ZeRO-1
+style).  World size 1 runs the same kernels degenerate (W=1), which is what the single
+GPU numerics tests exercise.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..build import lib_path
+from .collectives import Hyper
+
+ONESHOT_MAX_BYTES = 256 * 1024
+c_void_p, c_int, c_ll, c_float = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+
+
+class _RawCuda:
+    """Expose a raw device pointer through ``__cuda_array_interface__`` so torch can view it."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class _SymBuf:
+    def __init__(self, base: int, nbytes: int, peers: List[int], tensor: torch.Tensor):
+        self.base, self.nbytes, self.peers, self.tensor = base, nbytes, peers, tensor
+
+
+class PeerCollectives:
+    name = "peer"
+
+    def __init__(self, world, comm_blocks: int = 48):
+        if world.device.type != "cuda":
+            raise RuntimeError("PeerCollectives needs CUDA devices")
+        self.world, self.size, self.rank, self.device = world, world.size, world.rank, world.device
+        self.lib = ctypes.CDLL(lib_path())
+        self.lib.mpb_oneshot_max_elems.restype = c_ll
+        self.comm_blocks = comm_blocks
+        self.bufs: List[_SymBuf] = []
+        self.launches = 0
+        torch.cuda.set_device(self.device)
+        pad_bytes = self.lib.mpb_signal_pad_bytes()
+        self.pad = self._sym_alloc(pad_bytes)
+        self.epochs = torch.zeros(self.lib.mpb_epoch_bytes() // 4, dtype=torch.int32, device=self.device)
+        self._pads_arr = (c_void_p * self.size)(*self.pad.peers)
+        self._count_stage = self._sym_alloc(256)
+        if self.size > 1:
+            dist.barrier()
+
+    # ------------------------------------------------------------------ symmetric memory
+    def _sym_alloc(self, nbytes: int) -> _SymBuf:
+        nbytes = (int(nbytes) + 255) // 256 * 256
+        ptr = c_void_p()
+        rc = self.lib.mpb_sym_alloc(ctypes.byref(ptr), c_ll(nbytes))
+        if rc != 0:
+            raise RuntimeError("mpb_sym_alloc({}) failed: {}".format(nbytes, rc))
+        base = int(ptr.value)
+        peers = [base]
+        if self.size > 1:
+            hb = self.lib.mpb_ipc_handle_bytes()
+            hbuf = ctypes.create_string_buffer(hb)
+            rc = self.lib.mpb_ipc_get_handle(c_void_p(base), hbuf)
+            if rc != 0:
+                raise RuntimeError("cudaIpcGetMemHandle failed: {}".format(rc))
+            handles: List[Optional[bytes]] = [None] * self.size
+            dist.all_gather_object(handles, bytes(hbuf.raw))
+            peers = []
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    peers.append(base)
+                    continue
+                p = c_void_p()
+                rc = self.lib.mpb_ipc_open_handle(ctypes.create_string_buffer(h, hb), ctypes.byref(p))
+                if rc != 0:
+                    raise RuntimeError("cudaIpcOpenMemHandle(rank {}) failed: {}".format(r, rc))
+                peers.append(int(p.value))
+        t = torch.as_tensor(_RawCuda(base, nbytes), device=self.device)
+        buf = _SymBuf(base, nbytes, peers, t)
+        self.bufs.append(buf)
+        return buf
+
+    def alloc(self, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        esz = torch.empty((), dtype=dtype).element_size()
+        buf = self._sym_alloc(numel * esz)
+        return buf.tensor[: numel * esz].view(dtype)
+
+    def _peer_ptrs(self, view: Optional[torch.Tensor]):
+        """ctypes array of W pointers addressing ``view``'s range on every rank (or None)."""
+        if view is None:
+            return None
+        p = view.data_ptr()
+        for b in self.bufs:
+            if b.base <= p < b.base + b.nbytes:
+                off = p - b.base
+                return (c_void_p * self.size)(*[q + off for q in b.peers])
+        if self.size == 1:
+            return (c_void_p * 1)(p)
+        raise ValueError("tensor is not inside a symmetric arena obtained from PeerCollectives.alloc")
+
+    # ------------------------------------------------------------------ collectives
+    def _algo(self, algo: str, nbytes: int, numel: int) -> int:
+        if algo == "oneshot":
+            a = 0
+        elif algo in ("twoshot", "nvls"):
+            a = 1
+        else:
+            a = 0 if nbytes <= ONESHOT_MAX_BYTES else 1
+        if a == 0 and numel > self.lib.mpb_oneshot_max_elems(c_int(self._blocks(numel, 0))):
+            a = 1
+        return a
+
+    def _blocks(self, numel: int, algo: int) -> int:
+        per = 512 * 4
+        work = numel if algo == 0 else numel // max(self.size, 1)
+        need = max(1, (work + per - 1) // per)
+        cap = 128 if algo == 0 else self.comm_blocks
+        return int(min(cap, need))
+
+    def owns_full_state(self, algo: str) -> bool:
+        # conservative: any bucket that may run two-shot keeps sliced optimizer state
+        return self.size == 1
+
+    def _launch_ar(self, grads, params, shadows, m, v, hyper: Optional[Hyper], step: int, algo: str) -> None:
+        n = grads.numel()
+        a = self._algo(algo, n * 4, n)
+        blocks = self._blocks(n, a)
+        g = self._peer_ptrs(grads)
+        p = self._peer_ptrs(params)
+        s = self._peer_ptrs(shadows)
+        kind = 0 if hyper is None else (1 if hyper.kind == "adam" else 2)
+        h = hyper or Hyper()
+        rc = self.lib.mpb_allreduce_fused(
+            g, p, s, self._pads_arr, c_void_p(self.epochs.data_ptr()),
+            c_void_p(0 if m is None else m.data_ptr()), c_void_p(0 if v is None else v.data_ptr()),
+            c_ll(n), c_int(self.rank), c_int(self.size), c_int(a), c_int(blocks), c_int(kind), c_int(step),
+            c_float(h.lr), c_float(h.beta1), c_float(h.beta2), c_float(h.eps), c_float(h.weight_decay),
+            c_float(h.momentum), c_void_p(torch.cuda.current_stream().cuda_stream))
+        self.launches += 1
+        if rc != 0:
+            raise RuntimeError("mpb_allreduce_fused failed: {}".format(rc))
+
+    def all_reduce_avg_(self, view: torch.Tensor, algo: str = "auto") -> None:
+        if view.dtype != torch.float32:
+            raise TypeError("peer all-reduce operates on fp32 arenas")
+        self._launch_ar(view, None, None, None, None, None, 1, algo)
+
+    def all_reduce_update_(self, grads, params, state: Dict[str, torch.Tensor], shadow, hyper: Hyper, step: int,
+                           algo: str = "auto") -> None:
+        if hyper.kind == "adam":
+            m, v = state["exp_avg"], state["exp_avg_sq"]
+        else:
+            m, v = state["momentum_buffer"], None
+        self._launch_ar(grads, params, shadow, m, v, hyper, step, algo)
+
+    def broadcast_(self, view: torch.Tensor, root: int = 0) -> None:
+        if self.size == 1:
+            return
+        nbytes = view.numel() * view.element_size()
+        if nbytes % 16 != 0:
+            raise ValueError("broadcast range must be a multiple of 16 bytes")
+        n_floats = nbytes // 4
+        rc = self.lib.mpb_broadcast(self._peer_ptrs(view), self._pads_arr, c_void_p(self.epochs.data_ptr()),
+                                    c_ll(n_floats), c_int(self.rank), c_int(self.size), c_int(root),
+                                    c_int(self._blocks(n_floats * self.size, 1)),
+                                    c_void_p(torch.cuda.current_stream().cuda_stream))
+        self.launches += 1
+        if rc != 0:
+            raise RuntimeError("mpb_broadcast failed: {}".format(rc))
+
+    def all_gather_slices_(self, view: torch.Tensor) -> None:
+        if self.size == 1:
+            return
+        # optimizer moments are ordinary (non-symmetric) tensors: stage through a symmetric scratch
+        n = view.numel()
+        if not hasattr(self, "_ag_stage") or self._ag_stage.numel() < n:
+            self._ag_stage = self.alloc(n, torch.float32)
+        stage = self._ag_stage[:n]
+        stage.copy_(view)
+        rc = self.lib.mpb_allgather_slices(self._peer_ptrs(stage), self._pads_arr, c_void_p(self.epochs.data_ptr()),
+                                           c_ll(n), c_int(self.rank), c_int(self.size), c_int(self._blocks(n, 1)),
+                                           c_void_p(torch.cuda.current_stream().cuda_stream))
+        self.launches += 1
+        if rc != 0:
+            raise RuntimeError("mpb_allgather_slices failed: {}".format(rc))
+        view.copy_(stage)
+
+    def all_reduce_sum_i64(self, value: torch.Tensor) -> torch.Tensor:
+        stage = self._count_stage.tensor[:8].view(torch.int64)
+        stage.copy_(value.reshape(1))
+        out = torch.empty(1, dtype=torch.int64, device=self.device)
+        vals = (c_void_p * self.size)(*self._count_stage.peers)
+        rc = self.lib.mpb_count_allreduce(vals, self._pads_arr, c_void_p(self.epochs.data_ptr()),
+                                          c_void_p(out.data_ptr()), c_int(self.rank), c_int(self.size),
+                                          c_void_p(torch.cuda.current_stream().cuda_stream))
+        self.launches += 1
+        if rc != 0:
+            raise RuntimeError("mpb_count_allreduce failed: {}".format(rc))
+        value.copy_(out.reshape(value.shape))
+        return value
+
+    def barrier(self) -> None:
+        torch.cuda.synchronize(self.device)
+        if self.size > 1:
+            dist.barrier()
+
+    def sync_stream(self) -> None:
+        torch.cuda.current_stream(self.device).synchronize()
+
+    def close(self) -> None:
+        # allocations live for the life of the process (peers may still hold mappings); nothing to do
+        pass
