@@ -167,6 +167,8 @@ def run_ours(args) -> None:
         n = 0
         if cuda and ops.native_enabled():
             n += ops.native().LAUNCHES["n"]
+            from mpi_pytorch_b200.ops import tc
+            n += tc.LAUNCHES["n"]
         n += getattr(tr.engine.coll, "launches", 0)
         return n
 

@@ -3,7 +3,7 @@
 Every ``csrc/*.cu`` is compiled with ``nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo``
 (sm_100a only -- there is no multi-arch fat binary and no fallback path) into one shared object
 with a plain C ABI (``include/mpb200.h``), loaded through ``ctypes`` by
-``mpi_pytorch_b200/ops/native.py`` and ``parallel/peer.py``.  nvcc cross-compiles without a GPU, so
+``mpi_pytorch_b200/ops/cuda_impl.py`` and ``parallel/peer.py``.  nvcc cross-compiles without a GPU, so
 ``build()`` runs on the CPU-only build box; the resulting ``.so`` travels to the GPU box in-tree.
 """
 from __future__ import annotations

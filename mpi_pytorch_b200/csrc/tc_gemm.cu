@@ -1,0 +1,546 @@
+// K3-K6: tensor-core GEMM and implicit-GEMM convolution for sm_100a, hand-written with
+// tcgen05.mma (accumulators in TMEM), TMA (cp.async.bulk.tensor, tiled and im2col modes) and mbarrier
+// pipelines.  Replaces the ATen CPU conv / addmm calls the reference reaches from every nn.Conv2d and
+// nn.Linear: fprop, dgrad, wgrad and the linear fwd/dX/dW GEMMs, bf16 in, fp32
+// accumulate.  No cuDNN / cuBLAS / CUTLASS on this path.
+//
+// One CTA computes one 128 x BN output tile (BN in {32..256}).  Warp roles (192 threads):
+//   warp 0   : TMA producer  -- fills a kStages-deep ring of {A tile 128x64, B tile BNx64} bf16 in
+//              128B-swizzled shared memory; completion via mbarrier complete_tx
+//   warp 1   : TMEM allocator + MMA issuer -- one elected lane issues 4 x tcgen05.mma (K=16) per stage,
+//              tcgen05.commit releases the smem stage and finally signals the epilogue
+//   warps 2-5: epilogue -- tcgen05.ld the fp32 accumulator (lane = output row), add bias, optionally
+//              accumulate per-channel sum / sum-of-squares for BatchNorm, convert, store (or fp32
+//              atomic-add for split-K wgrad)
+//
+// The same kernel serves every problem; only the producer's coordinate generation changes:
+//   GEMM      : A[M,K], B[N,K] each either K-major ([rows][K]) or MN-major ([K][rows])
+//   conv fprop: A = im2col(x)  via TMA im2col mode (NHWC, C%64==0), B = W[Cout][R*S*C] K-major
+//   conv dgrad: A = im2col(dy) (stride-1 convs; flipped taps), B = W read as MN-major (no transpose copy)
+//   conv wgrad: A = dy^T MN-major, B = im2col(x) MN-major, reduction over output pixels, split-K
+//
+// UMMA shared-memory descriptor (64-bit), SWIZZLE_128B, bf16:
+//   K-major  tile [rows][64]: rows of 128 B; 8-row groups 1024 B apart (SBO=1024); +32 B per K=16 step
+//   MN-major tile [64 k][64 mn] regions: rows (k) of 128 B; 8-k groups 1024 B apart (SBO=1024);
+//            64-wide mn regions LBO bytes apart (LBO = 8192); +2048 B per K=16 step
+#include <cuda.h>
+#include "common.cuh"
+
+using namespace mpb;
+
+namespace {
+
+constexpr int BM = 128, BK = 64, kThreads = 192;
+constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
+
+// ------------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@P1 bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred P1;\n\t"
+      "elect.sync _|P1, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P1;\n\t"
+      "}" : "=r"(pred));
+  return pred != 0;
+}
+
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col_4d(const CUtensorMap* map, uint64_t* bar, void* dst, int c, int w, int h,
+                                                   int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h) : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// 64-bit UMMA smem descriptor: addr>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) | version=1 [46,48) | SWIZZLE_128B=2 [61,64)
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+enum Mode { MODE_GEMM = 0, MODE_FPROP = 1, MODE_DGRAD = 2, MODE_WGRAD = 3 };
+enum OutMode { OUT_BF16 = 0, OUT_F32 = 1, OUT_ATOMIC_F32 = 2 };
+
+struct TcParams {
+  int mode;
+  int M, N;                 // output tile space (rows, cols)
+  int BN;                   // tile width (multiple of 16, <= 256)
+  int a_mn, b_mn;           // operand majorness
+  int num_kb;               // total K blocks (of 64)
+  int kb_per_split;         // K blocks per blockIdx.z
+  uint32_t idesc;
+  int out_mode;
+  void* D; long long ldd;   // output, row stride in elements
+  const float* bias;        // [N] or null
+  float* stats;             // [2*N] per-channel sum / sumsq of the fp32 accumulator, or null
+  // conv geometry (im2col coordinate generation)
+  int C, R, S;              // reduction channels per tap (fprop: Cin, dgrad: Cout), filter size
+  int Hout, Wout;           // spatial size of the GEMM-M pixel space (fprop: P,Q; dgrad: H,W; wgrad: P,Q)
+  int stride, pad_h, pad_w, dil;
+  int tap_cols;             // wgrad: grid.y enumerates (tap, c-block); number of c-blocks per tap
+  int Cin_total;            // wgrad: Cin (row stride pieces of dW)
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // carve: [stages][A 16KB][B BN*128B] | barriers
+  const int b_stage_bytes = p.BN * BK * 2;
+  const int stage_bytes = A_STAGE_BYTES + b_stage_bytes;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  __shared__ uint64_t full_bar[8], empty_bar[8], tmem_full_bar;
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ float stat_smem[2][256];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int stages = (p.BN <= 64) ? 8 : (p.BN <= 128 ? 6 : 4);
+  const int m0 = blockIdx.x * BM;
+  int n0 = blockIdx.y * p.BN;
+  int tap_fixed = 0, cblk_fixed = 0;
+  if (p.mode == MODE_WGRAD) {           // grid.y = (tap, c-block)
+    tap_fixed = blockIdx.y / p.tap_cols;
+    cblk_fixed = blockIdx.y % p.tap_cols;
+    n0 = 0;
+  }
+  const int kb_begin = blockIdx.z * p.kb_per_split;
+  const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+  const int nkb = kb_end - kb_begin;
+  uint32_t tmem_cols = 32;
+  while ((int)tmem_cols < p.BN) tmem_cols <<= 1;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(&tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (p.stats) for (int j = threadIdx.x; j < 256; j += blockDim.x) { stat_smem[0][j] = 0.f; stat_smem[1][j] = 0.f; }
+  if (warp == 1) tmem_alloc(&tmem_base_smem, tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (nkb > 0) {
+    if (warp == 0) {
+      // ================================ TMA producer ================================
+      if (elect_one()) {
+        // pixel decomposition of the tile's first row (fprop / dgrad)
+        int q0 = 0, p0 = 0, img0 = 0;
+        if (p.mode == MODE_FPROP || p.mode == MODE_DGRAD) {
+          q0 = m0 % p.Wout;
+          const int t = m0 / p.Wout;
+          p0 = t % p.Hout;
+          img0 = t / p.Hout;
+        }
+        const int cblocks = p.C / BK;
+        for (int i = 0; i < nkb; ++i) {
+          const int kb = kb_begin + i;
+          const int st = i % stages;
+          const uint32_t ph = (i / stages) & 1;
+          mbar_wait(&empty_bar[st], ph ^ 1);
+          uint8_t* sa = smem + (size_t)st * stage_bytes;
+          uint8_t* sb = sa + A_STAGE_BYTES;
+          mbar_expect_tx(&full_bar[st], (uint32_t)stage_bytes);
+          if (p.mode == MODE_GEMM) {
+            if (!p.a_mn) tma_load_2d(&tmA, &full_bar[st], sa, kb * BK, m0);
+            else { tma_load_2d(&tmA, &full_bar[st], sa, m0, kb * BK); tma_load_2d(&tmA, &full_bar[st], sa + 8192, m0 + 64, kb * BK); }
+            if (!p.b_mn) tma_load_2d(&tmB, &full_bar[st], sb, kb * BK, n0);
+            else for (int j = 0; j < p.BN / 64; ++j) tma_load_2d(&tmB, &full_bar[st], sb + j * 8192, n0 + j * 64, kb * BK);
+          } else if (p.mode == MODE_FPROP) {
+            const int tap = kb / cblocks, cb = kb % cblocks;
+            const int r = tap / p.S, s = tap % p.S;
+            tma_load_im2col_4d(&tmA, &full_bar[st], sa, cb * BK, q0 * p.stride - p.pad_w, p0 * p.stride - p.pad_h, img0,
+                               (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+            tma_load_2d(&tmB, &full_bar[st], sb, tap * p.C + cb * BK, n0);
+          } else if (p.mode == MODE_DGRAD) {
+            // A = im2col(dy) with pad' = (R-1) - pad, taps (r'', s''); B = W[k][r][s][c] with r = R-1-r'', MN-major
+            const int tap = kb / cblocks, cb = kb % cblocks;       // cblocks = Cout/64 here
+            const int rr = tap / p.S, ss = tap % p.S;
+            tma_load_im2col_4d(&tmA, &full_bar[st], sa, cb * BK, q0 - p.pad_w, p0 - p.pad_h, img0, (uint16_t)ss, (uint16_t)rr);
+            const int r = p.R - 1 - rr, s = p.S - 1 - ss;
+            const int col = (r * p.S + s) * p.Cin_total + n0;
+            for (int j = 0; j < p.BN / 64; ++j) tma_load_2d(&tmB, &full_bar[st], sb + j * 8192, col + j * 64, cb * BK);
+          } else {  // MODE_WGRAD: reduction over output pixels; kb = pixel chunk of 64
+            const int pix = kb * BK;
+            const int q = pix % p.Wout;
+            const int t = pix / p.Wout;
+            const int pp = t % p.Hout, img = t / p.Hout;
+            tma_load_2d(&tmA, &full_bar[st], sa, m0, pix);
+            tma_load_2d(&tmA, &full_bar[st], sa + 8192, m0 + 64, pix);
+            const int r = tap_fixed / p.S, s = tap_fixed % p.S;
+            for (int j = 0; j < p.BN / 64; ++j)
+              tma_load_im2col_4d(&tmB, &full_bar[st], sb + j * 8192, (cblk_fixed * (p.BN / 64) + j) * 64,
+                                 q * p.stride - p.pad_w, pp * p.stride - p.pad_h, img, (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+          }
+        }
+      }
+    } else if (warp == 1) {
+      // ================================ MMA issuer ================================
+      const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
+      const uint32_t a_step = p.a_mn ? 128u : 2u, b_step = p.b_mn ? 128u : 2u;   // descriptor advance per K=16 (16 B units)
+      for (int i = 0; i < nkb; ++i) {
+        const int st = i % stages;
+        const uint32_t ph = (i / stages) & 1;
+        mbar_wait(&full_bar[st], ph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t sa = smem_u32(smem + (size_t)st * stage_bytes);
+          const uint32_t sb = sa + A_STAGE_BYTES;
+          const uint64_t adesc = make_desc(sa, a_lbo, 1024), bdesc = make_desc(sb, b_lbo, 1024);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16(tmem_base, adesc + (uint64_t)(a_step * k), bdesc + (uint64_t)(b_step * k), p.idesc, (i | k) != 0);
+          umma_commit(&empty_bar[st]);                 // frees the smem stage once these MMAs retire
+          if (i == nkb - 1) umma_commit(&tmem_full_bar);
+        }
+        __syncwarp();
+      }
+    } else {
+      // ================================ epilogue ================================
+      mbar_wait(&tmem_full_bar, 0);
+      tc_fence_after();
+      const int quarter = warp & 3;                      // TMEM lane quarter this warp may access
+      const int row = m0 + quarter * 32 + lane;
+      const bool row_ok = row < p.M;
+      int col_base = n0;
+      long long out_off = 0;
+      if (p.mode == MODE_WGRAD) { col_base = 0; out_off = (long long)tap_fixed * p.Cin_total + (long long)cblk_fixed * p.BN; }
+      for (int c = 0; c < p.BN; c += 32) {
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c, r);
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) if (col_base + c + j < p.N) v[j] += p.bias[col_base + c + j];
+        }
+        if (p.stats) {
+          // per-column sums over this warp's 32 rows: transpose-reduce (31 shuffles per quantity)
+          float s1[32], s2[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { const float x = row_ok ? v[j] : 0.f; s1[j] = x; s2[j] = x * x; }
+#pragma unroll
+          for (int off = 16; off >= 1; off >>= 1) {
+            const bool upper = (lane & off) != 0;
+#pragma unroll
+            for (int j = 0; j < off; ++j) {
+              // lane keeps columns [j + (upper?off:0)], sends the other half
+              const float send1 = upper ? s1[j] : s1[j + off], send2 = upper ? s2[j] : s2[j + off];
+              const float keep1 = upper ? s1[j + off] : s1[j], keep2 = upper ? s2[j + off] : s2[j];
+              s1[j] = keep1 + __shfl_xor_sync(0xffffffffu, send1, off);
+              s2[j] = keep2 + __shfl_xor_sync(0xffffffffu, send2, off);
+            }
+          }
+          // lane L now holds the total of column bitrev-free index: column = L (see derivation in DESIGN.md)
+          atomicAdd(&stat_smem[0][c + lane], s1[0]);
+          atomicAdd(&stat_smem[1][c + lane], s2[0]);
+        }
+        if (row_ok) {
+          const int ncols = min(32, p.N - (col_base + c));
+          if (ncols > 0) {
+            if (p.out_mode == OUT_BF16) {
+              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + (long long)row * p.ldd + out_off + col_base + c;
+              if (ncols == 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                  uint4 u;
+                  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
+                  h[0] = __floats2bfloat162_rn(v[j], v[j + 1]); h[1] = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+                  h[2] = __floats2bfloat162_rn(v[j + 4], v[j + 5]); h[3] = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+                  *reinterpret_cast<uint4*>(dst + j) = u;
+                }
+              } else {
+                for (int j = 0; j < ncols; ++j) dst[j] = __float2bfloat16_rn(v[j]);
+              }
+            } else if (p.out_mode == OUT_F32) {
+              float* dst = reinterpret_cast<float*>(p.D) + (long long)row * p.ldd + out_off + col_base + c;
+              if (ncols == 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              } else {
+                for (int j = 0; j < ncols; ++j) dst[j] = v[j];
+              }
+            } else {
+              float* dst = reinterpret_cast<float*>(p.D) + (long long)row * p.ldd + out_off + col_base + c;
+              for (int j = 0; j < ncols; ++j) atomicAdd(dst + j, v[j]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+    }
+  }
+  __syncthreads();
+  if (p.stats && nkb > 0) {
+    for (int j = threadIdx.x; j < p.BN; j += blockDim.x) {
+      if (n0 + j < p.N) {
+        atomicAdd(p.stats + n0 + j, stat_smem[0][j]);
+        atomicAdd(p.stats + p.N + n0 + j, stat_smem[1][j]);
+      }
+    }
+  }
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ host side
+typedef CUresult (*PFN_EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*PFN_EncodeIm2col)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                     const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+PFN_EncodeTiled g_encode_tiled = nullptr;
+PFN_EncodeIm2col g_encode_im2col = nullptr;
+
+int load_driver_fns() {
+  if (g_encode_tiled && g_encode_im2col) return 0;
+  cudaDriverEntryPointQueryResult q;
+  void* f = nullptr;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess || !f) return -10;
+  g_encode_tiled = (PFN_EncodeTiled)f;
+  f = nullptr;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &f, cudaEnableDefault, &q) != cudaSuccess || !f) return -11;
+  g_encode_im2col = (PFN_EncodeIm2col)f;
+  return 0;
+}
+
+// 2-D bf16 tensor [rows][cols] (cols contiguous, row stride ld elements); box = {box_cols, box_rows}
+int make_map_2d(CUtensorMap* m, const void* ptr, long long rows, long long cols, long long ld, int box_cols, int box_rows) {
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -(100 + (int)r);
+}
+
+// im2col map over an NHWC bf16 tensor: dims {C, W, H, N}; 64 channels x `pixels` output pixels per load.
+int make_map_im2col(CUtensorMap* m, const void* ptr, int N, int H, int W, int C, int lower_w, int lower_h, int upper_w,
+                    int upper_h, int stride, int pixels) {
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  int lower[2] = {lower_w, lower_h};
+  int upper[2] = {upper_w, upper_h};
+  cuuint32_t es[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUresult r = g_encode_im2col(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, lower, upper,
+                               (cuuint32_t)BK, (cuuint32_t)pixels, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -(200 + (int)r);
+}
+
+uint32_t make_idesc(int BN, int a_mn, int b_mn) {
+  uint32_t d = 0;
+  d |= 1u << 4;                    // D format F32
+  d |= 1u << 7;                    // A format BF16
+  d |= 1u << 10;                   // B format BF16
+  d |= (uint32_t)(a_mn ? 1 : 0) << 15;
+  d |= (uint32_t)(b_mn ? 1 : 0) << 16;
+  d |= (uint32_t)(BN >> 3) << 17;
+  d |= (uint32_t)(BM >> 4) << 24;
+  return d;
+}
+
+int smem_bytes_for(int BN) {
+  const int stages = (BN <= 64) ? 8 : (BN <= 128 ? 6 : 4);
+  return stages * (A_STAGE_BYTES + BN * BK * 2) + 1024;
+}
+
+int launch(const CUtensorMap& a, const CUtensorMap& b, const TcParams& p, dim3 grid, cudaStream_t st) {
+  const int smem = smem_bytes_for(p.BN);
+  static int configured = 0;
+  if (configured < smem) {
+    cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 1024);
+    if (e != cudaSuccess) return (int)e;
+    configured = 200 * 1024 + 1024;
+  }
+  tc_gemm_kernel<<<grid, kThreads, smem, st>>>(a, b, p);
+  return (int)cudaGetLastError();
+}
+
+int pick_bn(int n) {
+  if (n % 128 == 0 || n > 192) return 128;
+  if (n > 64) return 128;
+  if (n > 32) return 64;
+  return 32;
+}
+
+}  // namespace
+
+// D[M,N] = A[M,K] * B[N,K]^T   (bf16 operands, fp32 accumulate)
+//   a_mn = 0: A stored [M][K] (row stride lda)      a_mn = 1: A stored [K][M] (row stride lda)
+//   b_mn = 0: B stored [N][K] (row stride ldb)      b_mn = 1: B stored [K][N] (row stride ldb)
+//   out_mode 0: bf16 D, 1: fp32 D, 2: fp32 atomic accumulate with split-K (D must be pre-zeroed)
+MPB_API int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias, int M, int N, int K, long long lda,
+                        long long ldb, long long ldd, int a_mn, int b_mn, int out_mode, int splitk, void* stream) {
+  int rc = load_driver_fns();
+  if (rc) return rc;
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((lda % 8) || (ldb % 8) || ((uintptr_t)A & 15) || ((uintptr_t)B & 15)) return -2;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.mode = MODE_GEMM; p.M = M; p.N = N; p.BN = pick_bn(N); p.a_mn = a_mn; p.b_mn = b_mn;
+  if (b_mn && p.BN < 64) p.BN = 64;
+  p.num_kb = (K + BK - 1) / BK;
+  if (splitk < 1) splitk = 1;
+  if (out_mode != OUT_ATOMIC_F32) splitk = 1;
+  p.kb_per_split = (p.num_kb + splitk - 1) / splitk;
+  p.idesc = make_idesc(p.BN, a_mn, b_mn);
+  p.out_mode = out_mode; p.D = D; p.ldd = ldd; p.bias = bias;
+  CUtensorMap ta, tb;
+  rc = a_mn ? make_map_2d(&ta, A, K, M, lda, 64, 64) : make_map_2d(&ta, A, M, K, lda, 64, BM);
+  if (rc) return rc;
+  rc = b_mn ? make_map_2d(&tb, B, K, N, ldb, 64, 64) : make_map_2d(&tb, B, N, K, ldb, 64, p.BN);
+  if (rc) return rc - 1000;
+  dim3 grid((M + BM - 1) / BM, (N + p.BN - 1) / p.BN, (p.num_kb + p.kb_per_split - 1) / p.kb_per_split);
+  return launch(ta, tb, p, grid, (cudaStream_t)stream);
+}
+
+// y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C]) (+bias); NHWC bf16; C % 64 == 0, K % 16 == 0.
+// stats (optional): fp32 [2*K], must be zeroed by the caller; receives per-channel sum / sum of squares of y (fp32).
+MPB_API int mpb_tc_conv_fprop(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H, int W,
+                              int C, int K, int R, int S, int P, int Q, int stride, int pad_h, int pad_w, int dil,
+                              void* stream) {
+  int rc = load_driver_fns();
+  if (rc) return rc;
+  if (C % 64 != 0 || K % 16 != 0) return -2;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.mode = MODE_FPROP; p.M = N * P * Q; p.N = K; p.BN = pick_bn(K);
+  p.num_kb = R * S * (C / 64); p.kb_per_split = p.num_kb;
+  p.idesc = make_idesc(p.BN, 0, 0);
+  p.out_mode = OUT_BF16; p.D = y; p.ldd = K; p.bias = bias; p.stats = stats;
+  p.C = C; p.R = R; p.S = S; p.Hout = P; p.Wout = Q; p.stride = stride; p.pad_h = pad_h; p.pad_w = pad_w; p.dil = dil;
+  CUtensorMap ta, tb;
+  rc = make_map_im2col(&ta, x, N, H, W, C, -pad_w, -pad_h, pad_w - (S - 1) * dil, pad_h - (R - 1) * dil, stride, BM);
+  if (rc) return rc;
+  rc = make_map_2d(&tb, w, K, (long long)R * S * C, (long long)R * S * C, 64, p.BN);
+  if (rc) return rc - 1000;
+  dim3 grid((p.M + BM - 1) / BM, (K + p.BN - 1) / p.BN, 1);
+  return launch(ta, tb, p, grid, (cudaStream_t)stream);
+}
+
+// dx[N,H,W,C] = conv_transpose(dy[N,P,Q,K], w[K,R,S,C]) for stride-1, dilation-1 convolutions (P = H + 2*pad - R + 1).
+MPB_API int mpb_tc_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int K, int R, int S,
+                              int P, int Q, int pad_h, int pad_w, void* stream) {
+  int rc = load_driver_fns();
+  if (rc) return rc;
+  if (K % 64 != 0 || C % 64 != 0) return -2;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.mode = MODE_DGRAD; p.M = N * H * W; p.N = C; p.BN = (C % 128 == 0) ? 128 : 64; p.a_mn = 0; p.b_mn = 1;
+  p.num_kb = R * S * (K / 64); p.kb_per_split = p.num_kb;
+  p.idesc = make_idesc(p.BN, 0, 1);
+  p.out_mode = OUT_BF16; p.D = dx; p.ldd = C;
+  p.C = K; p.R = R; p.S = S; p.Hout = H; p.Wout = W; p.stride = 1; p.dil = 1; p.Cin_total = C;
+  p.pad_h = (R - 1) - pad_h; p.pad_w = (S - 1) - pad_w;
+  CUtensorMap ta, tb;
+  // gemm-M space is the H x W input grid: lower corner = pad - (S-1) = -pad', upper corner = lower + (W - Q)
+  // (so that Q + upper - lower == W base pixels per row), cf. the dgrad corner rules of TMA im2col.
+  rc = make_map_im2col(&ta, dy, N, P, Q, K, -p.pad_w, -p.pad_h, pad_w - (S - 1) + (W - Q), pad_h - (R - 1) + (H - P), 1, BM);
+  if (rc) return rc;
+  rc = make_map_2d(&tb, w, K, (long long)R * S * C, (long long)R * S * C, 64, 64);
+  if (rc) return rc - 1000;
+  dim3 grid((p.M + BM - 1) / BM, (C + p.BN - 1) / p.BN, 1);
+  return launch(ta, tb, p, grid, (cudaStream_t)stream);
+}
+
+// dw[K,R,S,C] (fp32, pre-zeroed) += sum over pixels dy[n,p,q,k] * x[n, p*stride+r-pad, q*stride+s-pad, c]
+MPB_API int mpb_tc_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R, int S,
+                              int P, int Q, int stride, int pad_h, int pad_w, int dil, int splitk, void* stream) {
+  int rc = load_driver_fns();
+  if (rc) return rc;
+  if (C % 64 != 0 || K % 8 != 0) return -2;
+  const long long npq = (long long)N * P * Q;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.mode = MODE_WGRAD; p.M = K; p.N = C; p.BN = (C % 128 == 0) ? 128 : 64; p.a_mn = 1; p.b_mn = 1;
+  p.num_kb = (int)((npq + BK - 1) / BK);
+  if (splitk < 1) splitk = 1;
+  p.kb_per_split = (p.num_kb + splitk - 1) / splitk;
+  p.idesc = make_idesc(p.BN, 1, 1);
+  p.out_mode = OUT_ATOMIC_F32; p.D = dw; p.ldd = (long long)R * S * C;
+  p.C = C; p.R = R; p.S = S; p.Hout = P; p.Wout = Q; p.stride = stride; p.pad_h = pad_h; p.pad_w = pad_w; p.dil = dil;
+  p.tap_cols = C / p.BN; p.Cin_total = C;
+  CUtensorMap ta, tb;
+  rc = make_map_2d(&ta, dy, npq, K, K, 64, 64);
+  if (rc) return rc;
+  rc = make_map_im2col(&tb, x, N, H, W, C, -pad_w, -pad_h, pad_w - (S - 1) * dil, pad_h - (R - 1) * dil, stride, BK);
+  if (rc) return rc - 1000;
+  dim3 grid((K + BM - 1) / BM, R * S * p.tap_cols, (p.num_kb + p.kb_per_split - 1) / p.kb_per_split);
+  return launch(ta, tb, p, grid, (cudaStream_t)stream);
+}

@@ -1,10 +1,10 @@
 """Functional op API of the framework.
 
 On CUDA tensors every function runs a hand-written sm_100a kernel from
-``mpi_pytorch_b200/csrc`` (through :mod:`.native`); on CPU tensors it runs the plain
+``mpi_pytorch_b200/csrc`` (through :mod:`.cuda_impl`, reached as ``ops.native()``); on CPU tensors it runs the plain
 torch implementation in :mod:`.reference`, which is also the oracle the kernels are
 tested against.  There is no silent CUDA fallback: if the extension is missing on a
-GPU box the import of :mod:`.native` raises (set ``MPB_NATIVE_OPS=0`` to run the
+GPU box the import of :mod:`.cuda_impl` raises (set ``MPB_NATIVE_OPS=0`` to run the
 torch/cuDNN baseline path deliberately, e.g. for the DDP comparison).
 """
 from __future__ import annotations
@@ -31,8 +31,8 @@ def native_enabled() -> bool:
 def native():
     """The loaded extension wrapper (imports / builds it on first use)."""
     if _STATE["native"] is None:
-        from . import native as _n
-        _STATE["native"] = _n
+        import importlib
+        _STATE["native"] = importlib.import_module(".cuda_impl", __name__)
     return _STATE["native"]
 
 

@@ -90,13 +90,14 @@ class _ConvFn(torch.autograd.Function):
         ctx.conf = (stride, padding, dilation, groups, bias is not None, weight.dtype)
         tc = _gemm()
         stats = None
-        if tc.conv_supported(x, w, stride, padding, dilation, groups):
+        if tc.fprop_ok(x, w, stride, padding, dilation, groups):
             y, stats = tc.conv_fprop(x, w, None if bias is None else bias.detach(), stride, padding, want_stats)
         else:
             _note_fallback("conv_fprop")
             b = None if bias is None else bias.detach().to(x.dtype)
-            y = F.conv2d(x, w, b, stride, padding, dilation, groups)
-            y = _nhwc(y)
+            y = _nhwc(F.conv2d(x, w, b, stride, padding, dilation, groups))
+            if want_stats:
+                stats = bn_stats(y)
         ctx.mark_non_differentiable(*([stats] if stats is not None else []))
         if want_stats:
             return y, stats
@@ -110,18 +111,24 @@ class _ConvFn(torch.autograd.Function):
         need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         tc = _gemm()
         gx = gw = gb = None
-        if tc.conv_supported(x, w, stride, padding, dilation, groups):
-            if need_x:
-                gx = tc.conv_dgrad(gy, w, x.shape, stride, padding)
-            if need_w:
-                gw = tc.conv_wgrad(gy, x, w.shape, stride, padding).to(wdtype)
-        else:
-            _note_fallback("conv_bwd")
-            gx, gw, _ = torch.ops.aten.convolution_backward(
+        args = (x, w, stride, padding, dilation, groups)
+        if need_x and tc.dgrad_ok(*args):
+            gx = tc.conv_dgrad(gy, w, x.shape, stride, padding)
+            need_x = False
+        if need_w and tc.wgrad_ok(*args):
+            gw = tc.conv_wgrad(gy, x, w.shape, stride, padding).to(wdtype)
+            need_w = False
+        if need_x or need_w:
+            _note_fallback("conv_dgrad" if need_x else "conv_wgrad")
+            if need_x and need_w:
+                _note_fallback("conv_wgrad")
+            fx, fw, _ = torch.ops.aten.convolution_backward(
                 gy, x, w, None, list(stride), list(padding), list(dilation), False, [0, 0], groups,
                 [need_x, need_w, False])
-            if gw is not None:
-                gw = gw.to(wdtype)
+            if need_x:
+                gx = fx
+            if need_w:
+                gw = fw.to(wdtype)
         if has_bias and ctx.needs_input_grad[2]:
             gb = gy.float().sum(dim=(0, 2, 3))
         return gx, gw, gb, None, None, None, None, None
@@ -215,6 +222,14 @@ class _BNActFn(torch.autograd.Function):
         if has_res and not relu:
             dres = gz
         return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None
+
+
+def bn_stats(y: torch.Tensor) -> torch.Tensor:
+    """Per-channel (sum, sum of squares) of an NHWC tensor -> fp32 [2C] (what the conv epilogue fuses)."""
+    n, c, h, w = y.shape
+    sums = torch.empty(2 * c, dtype=torch.float32, device=y.device)
+    _call("mpb_bn_stats", _p(y), _p(sums), c_ll(n * h * w), c_int(c), c_int(_dt(y)), c_void_p(_stream()), launches=2)
+    return sums
 
 
 def _bn_ok(x, bn) -> bool:

@@ -1,21 +1,146 @@
 """Tensor-core (tcgen05 / TMEM / TMA) GEMM and implicit-GEMM convolution front end.
 
-``*_supported`` decide whether a call can run on the hand-written sm_100a kernels in
-``csrc/tc_gemm.cu``; anything else is counted as a fallback by ``ops.native`` and runs on the
-library kernel.  Filled in by the K3-K6 work (see DESIGN.md for the status table).
+Python face of ``csrc/tc_gemm.cu``.  ``*_ok`` predicates say whether a call can run on the
+hand-written sm_100a kernel; anything else is counted as a library fallback by ``ops.cuda_impl``.
+Conventions: activations NHWC (channels-last) bf16, conv weights logical (K,C,R,S) with physical
+KRSC (channels-last), fp32 accumulation everywhere; weight gradients come back in fp32.
 """
 from __future__ import annotations
 
+import ctypes
 import os
+from typing import Optional, Tuple
 
 import torch
 
+from ..build import lib_path
+
 ENABLED = os.environ.get("MPB_TC", "1").lower() not in ("0", "false", "off")
+_LIB = ctypes.CDLL(lib_path())
+LAUNCHES = {"n": 0}
+c_void_p, c_int, c_ll = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong
+SMS = 148
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]):
+    return c_void_p(0 if t is None else t.data_ptr())
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError("{} failed with code {}".format(what, rc))
+
+
+# ----------------------------------------------------------------------------------------------- GEMM
+def gemm(a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int, a_mn: bool, b_mn: bool,
+         bias: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16, splitk: int = 1) -> torch.Tensor:
+    """D[m,n] = A[m,k] @ B[n,k]^T.  ``a`` is stored [m][k] (a_mn False) or [k][m] (True); same for ``b``."""
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_contiguous() and b.is_contiguous()
+    if splitk > 1:
+        d = torch.zeros((m, n), dtype=torch.float32, device=a.device)
+        mode = 2
+    else:
+        d = torch.empty((m, n), dtype=out_dtype, device=a.device)
+        mode = 0 if out_dtype == torch.bfloat16 else 1
+    rc = _LIB.mpb_tc_gemm(_p(a), _p(b), _p(d), _p(bias), c_int(m), c_int(n), c_int(k), c_ll(a.stride(0)),
+                          c_ll(b.stride(0)), c_ll(n), c_int(int(a_mn)), c_int(int(b_mn)), c_int(mode), c_int(splitk),
+                          c_void_p(_stream()))
+    LAUNCHES["n"] += 1
+    _check(rc, "mpb_tc_gemm")
+    return d if splitk == 1 or out_dtype == torch.float32 else d.to(out_dtype)
 
 
 def gemm_supported(x: torch.Tensor, w: torch.Tensor) -> bool:
-    return False
+    if not ENABLED or x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or x.dim() != 2:
+        return False
+    out_f, in_f = w.shape
+    return in_f % 8 == 0 and out_f % 8 == 0 and x.shape[0] % 8 == 0 and w.is_contiguous()
+
+
+def linear_fwd(x, w, bias):
+    return gemm(x, w, x.shape[0], w.shape[0], w.shape[1], False, False, None if bias is None else bias.float())
+
+
+def linear_dx(gy, w):
+    return gemm(gy, w, gy.shape[0], w.shape[1], w.shape[0], False, True)
+
+
+def linear_dw(gy, x):
+    return gemm(gy, x, gy.shape[1], x.shape[1], gy.shape[0], True, True, out_dtype=torch.float32)
+
+
+# ----------------------------------------------------------------------------------------------- conv
+def _geom(x_shape, w_shape, stride, padding):
+    n, c, h, w = x_shape
+    k, _, r, s = w_shape
+    p = (h + 2 * padding[0] - r) // stride[0] + 1
+    q = (w + 2 * padding[1] - s) // stride[1] + 1
+    return n, c, h, w, k, r, s, p, q
+
+
+def _base_ok(x, w, stride, padding, dilation, groups) -> bool:
+    if not ENABLED or groups != 1 or tuple(dilation) != (1, 1) or stride[0] != stride[1]:
+        return False
+    if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or x.dim() != 4:
+        return False
+    if not x.is_contiguous(memory_format=torch.channels_last) or not w.is_contiguous(memory_format=torch.channels_last):
+        return False
+    return x.data_ptr() % 16 == 0 and w.data_ptr() % 16 == 0
+
+
+def fprop_ok(x, w, stride, padding, dilation, groups) -> bool:
+    return _base_ok(x, w, stride, padding, dilation, groups) and x.shape[1] % 64 == 0 and w.shape[0] % 16 == 0
+
+
+def dgrad_ok(x, w, stride, padding, dilation, groups) -> bool:
+    return (_base_ok(x, w, stride, padding, dilation, groups) and stride[0] == 1 and x.shape[1] % 64 == 0
+            and w.shape[0] % 64 == 0 and padding[0] <= w.shape[2] - 1 and padding[1] <= w.shape[3] - 1)
+
+
+def wgrad_ok(x, w, stride, padding, dilation, groups) -> bool:
+    return _base_ok(x, w, stride, padding, dilation, groups) and x.shape[1] % 64 == 0 and w.shape[0] % 8 == 0
 
 
 def conv_supported(x, w, stride, padding, dilation, groups) -> bool:
-    return False
+    return fprop_ok(x, w, stride, padding, dilation, groups)
+
+
+def conv_fprop(x, w, bias, stride, padding, want_stats=False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    n, c, h, wd, k, r, s, p, q = _geom(x.shape, w.shape, stride, padding)
+    y = torch.empty((n, k, p, q), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    stats = torch.zeros(2 * k, dtype=torch.float32, device=x.device) if want_stats else None
+    rc = _LIB.mpb_tc_conv_fprop(_p(x), _p(w), _p(y), _p(None if bias is None else bias.float()), _p(stats), c_int(n),
+                                c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r), c_int(s), c_int(p), c_int(q),
+                                c_int(stride[0]), c_int(padding[0]), c_int(padding[1]), c_int(1), c_void_p(_stream()))
+    LAUNCHES["n"] += 1 + int(want_stats)
+    _check(rc, "mpb_tc_conv_fprop")
+    return y, stats
+
+
+def conv_dgrad(gy, w, x_shape, stride, padding) -> torch.Tensor:
+    n, c, h, wd, k, r, s, p, q = _geom(x_shape, w.shape, stride, padding)
+    dx = torch.empty(tuple(x_shape), dtype=torch.bfloat16, device=gy.device, memory_format=torch.channels_last)
+    rc = _LIB.mpb_tc_conv_dgrad(_p(gy), _p(w), _p(dx), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r),
+                                c_int(s), c_int(p), c_int(q), c_int(padding[0]), c_int(padding[1]), c_void_p(_stream()))
+    LAUNCHES["n"] += 1
+    _check(rc, "mpb_tc_conv_dgrad")
+    return dx
+
+
+def conv_wgrad(gy, x, w_shape, stride, padding) -> torch.Tensor:
+    n, c, h, wd, k, r, s, p, q = _geom(x.shape, w_shape, stride, padding)
+    dw = torch.zeros((k, r, s, c), dtype=torch.float32, device=gy.device)
+    bn = 128 if c % 128 == 0 else 64
+    tiles = ((k + 127) // 128) * r * s * (c // bn)
+    num_kb = (n * p * q + 63) // 64
+    splitk = max(1, min((SMS * 3 + tiles - 1) // tiles, max(1, num_kb // 4)))
+    rc = _LIB.mpb_tc_conv_wgrad(_p(gy), _p(x), _p(dw), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r),
+                                c_int(s), c_int(p), c_int(q), c_int(stride[0]), c_int(padding[0]), c_int(padding[1]),
+                                c_int(1), c_int(splitk), c_void_p(_stream()))
+    LAUNCHES["n"] += 2
+    _check(rc, "mpb_tc_conv_wgrad")
+    return dw.permute(0, 3, 1, 2)          # logical (K,C,R,S), physical KRSC

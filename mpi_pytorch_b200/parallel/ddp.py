@@ -143,7 +143,7 @@ class FusedDataParallel:
         if self.shadow_arena is not None:
             self.shadow_arena.copy_(self.param_arena)
             for p in self.layout.params:
-                p._mpb_shadow = self.layout.view(self.shadow_arena, p)      # bf16 compute copy read by ops.native
+                p._mpb_shadow = self.layout.view(self.shadow_arena, p)      # bf16 compute copy read by ops.cuda_impl
 
     def _reset_pending(self) -> None:
         for b in self.layout.buckets:

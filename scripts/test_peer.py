@@ -29,10 +29,6 @@ def main():
         want = g.clone()
         dist.all_reduce(want)
         want /= W
-        for rep in range(3):                         # back-to-back launches exercise flag reuse
-            g2 = g.clone() if rep else g
-            if rep:
-                g.copy_(want * 0 + g2)
         pc.all_reduce_avg_(g, algo)
         torch.cuda.synchronize()
         err = (g - want).abs().max().item()

@@ -110,11 +110,11 @@ def test_avgpool(k, s, p, ceil, cip):
     y = nat().avg_pool2d(x, k, s, p, ceil, cip)
     g = cl(torch.randn_like(y))
     y.backward(g)
-    xr = x.detach().clone().requires_grad_(True)
+    xr = x.detach().cpu().contiguous().double().requires_grad_(True)      # CPU fp64 oracle
     yr = F.avg_pool2d(xr, k, s, p, ceil, cip)
-    yr.backward(g)
-    assert torch.allclose(y, yr, atol=1e-5)
-    assert torch.allclose(x.grad, xr.grad, atol=1e-5)
+    yr.backward(g.cpu().contiguous().double())
+    assert torch.allclose(y.cpu().double(), yr, atol=1e-5)
+    assert torch.allclose(x.grad.cpu().double(), xr.grad, atol=1e-5)
 
 
 @pytest.mark.parametrize("out", [(1, 1), (6, 6), (7, 7)])
@@ -153,7 +153,7 @@ def test_adam_and_sgd_flat():
     for step in (1, 2, 3):
         nat().adam_flat(p, g, m, v, sh, step, 4e-4, 0.9, 0.999, 1e-8, 0.0)
         ref.adam_step(p2, g, m2, v2, step, 4e-4)
-    assert torch.allclose(p, p2, atol=1e-6) and torch.allclose(m, m2, atol=1e-6) and torch.allclose(v, v2, atol=1e-7)
+    assert torch.allclose(p, p2, atol=1e-6) and torch.allclose(m, m2, atol=1e-6) and torch.allclose(v, v2, atol=1e-9, rtol=1e-5)
     assert torch.equal(sh, p.bfloat16())
     q = torch.randn(n, device="cuda"); q2 = q.clone(); b = torch.zeros(n, device="cuda"); b2 = b.clone()
     for step in (1, 2):
