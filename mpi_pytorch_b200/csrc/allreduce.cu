@@ -147,33 +147,55 @@ __global__ void __launch_bounds__(MPB_COMM_THREADS, 1) allreduce_kernel(ArParams
       }
     }
   } else {
-    // ---- two-shot: my slice only; result pushed to every peer
+    // ---- two-shot: my slice only; result pushed to every peer.  U vectors per thread per trip keep
+    // 16 x 16 B peer loads in flight per thread (NVLink latency ~2-3 us needs ~2 MB in flight per GPU).
+    constexpr int U = (W <= 2) ? 8 : (W <= 4 ? 4 : 2);
     const long long slice4 = (P.n / W) >> 2;
     const long long base4 = slice4 * P.rank;
-    for (long long j = tid; j < slice4; j += nthreads) {
-      const long long i4 = base4 + j;
-      const float4 s = sum_peers<W>(P, i4);
-      if (P.opt.kind == 0) {
+    for (long long j0 = 0; j0 < slice4; j0 += nthreads * U) {
+      float4 acc[U];
+      float4 v[U][W];
 #pragma unroll
-        for (int p = 0; p < W; ++p) st_peer_f4(reinterpret_cast<float*>(P.grads.p[p]) + i4 * 4, s);
-      } else {
-        float* pp = reinterpret_cast<float*>(P.params.p[P.rank]) + i4 * 4;
-        float4 p4 = *reinterpret_cast<float4*>(pp);
-        float4 m4 = *reinterpret_cast<float4*>(P.m + i4 * 4);
-        float4 v4 = P.opt.kind == 1 ? *reinterpret_cast<float4*>(P.v + i4 * 4) : make_float4(0, 0, 0, 0);
-        p4.x = opt_one(p4.x, s.x, m4.x, v4.x, P.opt); p4.y = opt_one(p4.y, s.y, m4.y, v4.y, P.opt);
-        p4.z = opt_one(p4.z, s.z, m4.z, v4.z, P.opt); p4.w = opt_one(p4.w, s.w, m4.w, v4.w, P.opt);
-        *reinterpret_cast<float4*>(P.m + i4 * 4) = m4;
-        if (P.opt.kind == 1) *reinterpret_cast<float4*>(P.v + i4 * 4) = v4;
-        uint2 u;
-        *reinterpret_cast<__nv_bfloat162*>(&u.x) = __floats2bfloat162_rn(p4.x, p4.y);
-        *reinterpret_cast<__nv_bfloat162*>(&u.y) = __floats2bfloat162_rn(p4.z, p4.w);
+      for (int u = 0; u < U; ++u) {
+        const long long j = j0 + (long long)u * nthreads + tid;
+        if (j < slice4) {
 #pragma unroll
-        for (int p = 0; p < W; ++p) {
-          st_peer_f4(reinterpret_cast<float*>(P.params.p[p]) + i4 * 4, p4);
-          if (P.shadows.p[p]) st_peer_u2(reinterpret_cast<__nv_bfloat16*>(P.shadows.p[p]) + i4 * 4, u);
+          for (int p = 0; p < W; ++p) v[u][p] = ld_peer_f4(reinterpret_cast<const float*>(P.grads.p[p]) + (base4 + j) * 4);
         }
       }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long j = j0 + (long long)u * nthreads + tid;
+        if (j >= slice4) continue;
+        float4 s = v[u][0];
+#pragma unroll
+        for (int p = 1; p < W; ++p) { s.x += v[u][p].x; s.y += v[u][p].y; s.z += v[u][p].z; s.w += v[u][p].w; }
+        s.x *= P.scale; s.y *= P.scale; s.z *= P.scale; s.w *= P.scale;
+        acc[u] = s;
+        const long long i4 = base4 + j;
+        if (P.opt.kind == 0) {
+#pragma unroll
+          for (int p = 0; p < W; ++p) st_peer_f4(reinterpret_cast<float*>(P.grads.p[p]) + i4 * 4, s);
+        } else {
+          float* pp = reinterpret_cast<float*>(P.params.p[P.rank]) + i4 * 4;
+          float4 p4 = *reinterpret_cast<float4*>(pp);
+          float4 m4 = *reinterpret_cast<float4*>(P.m + i4 * 4);
+          float4 v4 = P.opt.kind == 1 ? *reinterpret_cast<float4*>(P.v + i4 * 4) : make_float4(0, 0, 0, 0);
+          p4.x = opt_one(p4.x, s.x, m4.x, v4.x, P.opt); p4.y = opt_one(p4.y, s.y, m4.y, v4.y, P.opt);
+          p4.z = opt_one(p4.z, s.z, m4.z, v4.z, P.opt); p4.w = opt_one(p4.w, s.w, m4.w, v4.w, P.opt);
+          *reinterpret_cast<float4*>(P.m + i4 * 4) = m4;
+          if (P.opt.kind == 1) *reinterpret_cast<float4*>(P.v + i4 * 4) = v4;
+          uint2 uu;
+          *reinterpret_cast<__nv_bfloat162*>(&uu.x) = __floats2bfloat162_rn(p4.x, p4.y);
+          *reinterpret_cast<__nv_bfloat162*>(&uu.y) = __floats2bfloat162_rn(p4.z, p4.w);
+#pragma unroll
+          for (int p = 0; p < W; ++p) {
+            st_peer_f4(reinterpret_cast<float*>(P.params.p[p]) + i4 * 4, p4);
+            if (P.shadows.p[p]) st_peer_u2(reinterpret_cast<__nv_bfloat16*>(P.shadows.p[p]) + i4 * 4, uu);
+          }
+        }
+      }
+      (void)acc;
     }
     rank_barrier(P.pads, P.rank, W, e0 + 2);          // every slice has landed everywhere
   }

@@ -18,11 +18,13 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const T* __restrict__ 
   const int cvecs = g.C / 8;
   const long long total = (long long)g.N * g.Ho * g.Wo * cvecs;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int cv = (int)(i % cvecs);
-    long long t = i / cvecs;
-    const int wo = (int)(t % g.Wo); t /= g.Wo;
-    const int ho = (int)(t % g.Ho);
-    const int n = (int)(t / g.Ho);
+    // 32-bit index math (64-bit div/mod costs ~100 instructions each and dominated this kernel)
+    const unsigned iu = (unsigned)i;
+    const int cv = (int)(iu % (unsigned)cvecs);
+    unsigned t = iu / (unsigned)cvecs;
+    const int wo = (int)(t % (unsigned)g.Wo); t /= (unsigned)g.Wo;
+    const int ho = (int)(t % (unsigned)g.Ho);
+    const int n = (int)(t / (unsigned)g.Ho);
     float best[8];
     unsigned char bi[8];
 #pragma unroll
@@ -55,11 +57,12 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ 
   const int cvecs = g.C / 8;
   const long long total = (long long)g.N * g.H * g.W * cvecs;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int cv = (int)(i % cvecs);
-    long long t = i / cvecs;
-    const int w = (int)(t % g.W); t /= g.W;
-    const int h = (int)(t % g.H);
-    const int n = (int)(t / g.H);
+    const unsigned iu = (unsigned)i;
+    const int cv = (int)(iu % (unsigned)cvecs);
+    unsigned t = iu / (unsigned)cvecs;
+    const int w = (int)(t % (unsigned)g.W); t /= (unsigned)g.W;
+    const int h = (int)(t % (unsigned)g.H);
+    const int n = (int)(t / (unsigned)g.H);
     float acc[8] = {0};
     // output windows containing (h, w): ho*sh - ph <= h < ho*sh - ph + kh
     int ho_lo = (h + g.ph - g.kh + g.sh) / g.sh; if (h + g.ph - g.kh + 1 <= 0) ho_lo = 0;
@@ -257,6 +260,7 @@ static PoolGeom geom(int N, int H, int W, int C, int Ho, int Wo, int kh, int kw,
 MPB_API int mpb_maxpool_fwd(const void* x, void* y, unsigned char* idx, int N, int H, int W, int C, int Ho, int Wo,
                             int kh, int kw, int sh, int sw, int ph, int pw, int dtype, void* stream) {
   if (C % 8 != 0 || kh * kw > 255) return -1;
+  if ((long long)N * H * W * (C / 8) >= (1ll << 32)) return -3;
   const PoolGeom g = geom(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw);
   const long long total = (long long)N * Ho * Wo * (C / 8);
   DISPATCH_T(dtype, maxpool_fwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, g);)

@@ -24,6 +24,7 @@
 //   MN-major tile [64 k][64 mn] regions: rows (k) of 128 B; 8-k groups 1024 B apart (SBO=1024);
 //            64-wide mn regions LBO bytes apart (LBO = 8192); +2048 B per K=16 step
 #include <cuda.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 using namespace mpb;
@@ -146,9 +147,10 @@ struct TcParams {
   int stride, pad_h, pad_w, dil;
   int tap_cols;             // wgrad: grid.y enumerates (tap, c-block); number of c-blocks per tap
   int Cin_total;            // wgrad: Cin (row stride pieces of dW)
+  int stages;               // smem ring depth (fewer stages -> more co-resident CTAs per SM)
 };
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 4)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages][A 16KB][B BN*128B] | barriers
@@ -160,7 +162,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __shared__ float stat_smem[2][256];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int stages = (p.BN <= 64) ? 8 : (p.BN <= 128 ? 6 : 4);
+  const int stages = p.stages;
   const int m0 = blockIdx.x * BM;
   int n0 = blockIdx.y * p.BN;
   int tap_fixed = 0, cblk_fixed = 0;
@@ -415,13 +417,23 @@ uint32_t make_idesc(int BN, int a_mn, int b_mn) {
   return d;
 }
 
-int smem_bytes_for(int BN) {
-  const int stages = (BN <= 64) ? 8 : (BN <= 128 ? 6 : 4);
-  return stages * (A_STAGE_BYTES + BN * BK * 2) + 1024;
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
 }
 
-int launch(const CUtensorMap& a, const CUtensorMap& b, const TcParams& p, dim3 grid, cudaStream_t st) {
-  const int smem = smem_bytes_for(p.BN);
+int default_stages(int BN, int num_kb) {
+  int s = env_int("MPB_TC_STAGES", 0);
+  if (s <= 0) s = 2;   // measured: co-resident CTAs (3-4 per SM) beat a deeper ring on every ResNet layer
+  if (s > 8) s = 8;
+  if (s > num_kb && num_kb > 0) s = num_kb < 2 ? 2 : num_kb;
+  while (s > 2 && s * (A_STAGE_BYTES + BN * BK * 2) + 1024 > 200 * 1024) --s;
+  return s;
+}
+
+int launch(const CUtensorMap& a, const CUtensorMap& b, TcParams p, dim3 grid, cudaStream_t st) {
+  p.stages = default_stages(p.BN, p.kb_per_split);
+  const int smem = p.stages * (A_STAGE_BYTES + p.BN * BK * 2) + 1024;
   static int configured = 0;
   if (configured < smem) {
     cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 1024);
@@ -433,6 +445,8 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, const TcParams& p, dim3 g
 }
 
 int pick_bn(int n) {
+  const int forced = env_int("MPB_TC_BN", 0);
+  if (forced > 0 && n % forced == 0) return forced;
   if (n % 128 == 0 || n > 192) return 128;
   if (n > 64) return 128;
   if (n > 32) return 64;

@@ -88,6 +88,7 @@ class _ConvFn(torch.autograd.Function):
         w = _compute_weight(weight, x.dtype)
         ctx.save_for_backward(x, w)
         ctx.conf = (stride, padding, dilation, groups, bias is not None, weight.dtype)
+        ctx.weight_param = weight if getattr(weight, "_mpb_grad_ready", None) is not None else None
         tc = _gemm()
         stats = None
         if tc.fprop_ok(x, w, stride, padding, dilation, groups):
@@ -116,7 +117,15 @@ class _ConvFn(torch.autograd.Function):
             gx = tc.conv_dgrad(gy, w, x.shape, stride, padding)
             need_x = False
         if need_w and tc.wgrad_ok(*args):
-            gw = tc.conv_wgrad(gy, x, w.shape, stride, padding).to(wdtype)
+            wp = ctx.weight_param
+            if wp is not None and wp.grad is not None and wp.grad.dtype == torch.float32 \
+                    and wp.grad.permute(0, 2, 3, 1).is_contiguous():
+                # accumulate straight into the parameter's slot of the (zeroed) gradient arena and tell the
+                # DP engine the gradient is complete; autograd sees "no gradient" for the weight
+                tc.conv_wgrad(gy, x, w.shape, stride, padding, out=wp.grad)
+                wp._mpb_grad_ready(wp)
+            else:
+                gw = tc.conv_wgrad(gy, x, w.shape, stride, padding).to(wdtype)
             need_w = False
         if need_x or need_w:
             _note_fallback("conv_dgrad" if need_x else "conv_wgrad")

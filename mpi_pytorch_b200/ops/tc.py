@@ -131,16 +131,21 @@ def conv_dgrad(gy, w, x_shape, stride, padding) -> torch.Tensor:
     return dx
 
 
-def conv_wgrad(gy, x, w_shape, stride, padding) -> torch.Tensor:
+def conv_wgrad(gy, x, w_shape, stride, padding, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp32 weight gradient.  With ``out`` (a zero-initialised or partially accumulated fp32 buffer in
+    physical KRSC order, e.g. the parameter's slot in the gradient arena) the split-K partial sums are
+    atomically accumulated straight into it -- no temporary, no separate add."""
     n, c, h, wd, k, r, s, p, q = _geom(x.shape, w_shape, stride, padding)
-    dw = torch.zeros((k, r, s, c), dtype=torch.float32, device=gy.device)
+    dw = torch.zeros((k, r, s, c), dtype=torch.float32, device=gy.device) if out is None else out
     bn = 128 if c % 128 == 0 else 64
     tiles = ((k + 127) // 128) * r * s * (c // bn)
     num_kb = (n * p * q + 63) // 64
-    splitk = max(1, min((SMS * 3 + tiles - 1) // tiles, max(1, num_kb // 4)))
+    splitk = max(1, min((SMS * 6 + tiles - 1) // tiles, max(1, num_kb // 4)))
     rc = _LIB.mpb_tc_conv_wgrad(_p(gy), _p(x), _p(dw), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r),
                                 c_int(s), c_int(p), c_int(q), c_int(stride[0]), c_int(padding[0]), c_int(padding[1]),
                                 c_int(1), c_int(splitk), c_void_p(_stream()))
-    LAUNCHES["n"] += 2
+    LAUNCHES["n"] += 2 if out is None else 1
     _check(rc, "mpb_tc_conv_wgrad")
+    if out is not None:
+        return out
     return dw.permute(0, 3, 1, 2)          # logical (K,C,R,S), physical KRSC

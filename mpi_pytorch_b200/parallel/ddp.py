@@ -144,6 +144,9 @@ class FusedDataParallel:
             self.shadow_arena.copy_(self.param_arena)
             for p in self.layout.params:
                 p._mpb_shadow = self.layout.view(self.shadow_arena, p)      # bf16 compute copy read by ops.cuda_impl
+        if self.device.type == "cuda":
+            for p in self.layout.params:
+                p._mpb_grad_ready = self._on_grad     # kernels that write p.grad in place report completion here
 
     def _reset_pending(self) -> None:
         for b in self.layout.buckets:

@@ -45,7 +45,7 @@ class _SymBuf:
 class PeerCollectives:
     name = "peer"
 
-    def __init__(self, world, comm_blocks: int = 48):
+    def __init__(self, world, comm_blocks: int = 64):
         if world.device.type != "cuda":
             raise RuntimeError("PeerCollectives needs CUDA devices")
         self.world, self.size, self.rank, self.device = world, world.size, world.rank, world.device
@@ -129,7 +129,7 @@ class PeerCollectives:
         per = 512 * 4
         work = numel if algo == 0 else numel // max(self.size, 1)
         need = max(1, (work + per - 1) // per)
-        cap = 128 if algo == 0 else self.comm_blocks
+        cap = 128 if (algo == 0 or self.size == 1) else self.comm_blocks
         return int(min(cap, need))
 
     def owns_full_state(self, algo: str) -> bool:

@@ -33,6 +33,13 @@ CONV_CASES = {
     "conv_l3": (8, 256, 14, 14, 256, 3, 1, 1),
     "conv_l4": (16, 512, 7, 7, 512, 3, 1, 1),
     "conv_nopad": (4, 64, 17, 17, 128, 3, 1, 0),
+    # full-size ResNet-34 layers at batch 256 (performance cases)
+    "full_l1": (256, 64, 56, 56, 64, 3, 1, 1),
+    "full_l2": (256, 128, 28, 28, 128, 3, 1, 1),
+    "full_l3": (256, 256, 14, 14, 256, 3, 1, 1),
+    "full_l4": (256, 512, 7, 7, 512, 3, 1, 1),
+    "full_l2_s2": (256, 64, 56, 56, 128, 3, 2, 1),
+    "full_l2_ds": (256, 64, 56, 56, 128, 1, 2, 0),
 }
 
 

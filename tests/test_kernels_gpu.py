@@ -153,7 +153,7 @@ def test_adam_and_sgd_flat():
     for step in (1, 2, 3):
         nat().adam_flat(p, g, m, v, sh, step, 4e-4, 0.9, 0.999, 1e-8, 0.0)
         ref.adam_step(p2, g, m2, v2, step, 4e-4)
-    assert torch.allclose(p, p2, atol=1e-6) and torch.allclose(m, m2, atol=1e-6) and torch.allclose(v, v2, atol=1e-9, rtol=1e-5)
+    assert torch.allclose(p, p2, atol=1e-6) and torch.allclose(m, m2, atol=1e-6) and torch.allclose(v, v2, atol=1e-8, rtol=1e-4)
     assert torch.equal(sh, p.bfloat16())
     q = torch.randn(n, device="cuda"); q2 = q.clone(); b = torch.zeros(n, device="cuda"); b2 = b.clone()
     for step in (1, 2):

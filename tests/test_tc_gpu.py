@@ -1,0 +1,95 @@
+"""tcgen05 GEMM / implicit-GEMM convolution vs an fp32 PyTorch oracle on the same bf16-rounded inputs."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _tc():
+    from mpi_pytorch_b200.ops import tc
+    return tc
+
+
+def _rel(a, b):
+    return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-12)).item()
+
+
+@pytest.mark.parametrize("m,n,k,a_mn,b_mn", [(128, 64, 64, 0, 0), (256, 1000, 512, 0, 0), (300, 136, 200, 0, 0),
+                                              (256, 512, 1000, 0, 1), (1000, 512, 256, 1, 1), (512, 256, 768, 1, 0)])
+def test_gemm_all_majorness(m, n, k, a_mn, b_mn):
+    torch.manual_seed(0)
+    a = torch.randn(m, k, device="cuda").bfloat16()
+    b = torch.randn(n, k, device="cuda").bfloat16()
+    ref = a.float() @ b.float().t()
+    a_st = a.t().contiguous() if a_mn else a
+    b_st = b.t().contiguous() if b_mn else b
+    d32 = _tc().gemm(a_st, b_st, m, n, k, bool(a_mn), bool(b_mn), out_dtype=torch.float32)
+    assert _rel(d32, ref) < 1e-5
+    bias = torch.randn(n, device="cuda")
+    d16 = _tc().gemm(a_st, b_st, m, n, k, bool(a_mn), bool(b_mn), bias=bias)
+    assert _rel(d16, ref + bias) < 1e-2
+
+
+def test_gemm_splitk_atomic():
+    a = torch.randn(128, 4096, device="cuda").bfloat16()
+    b = torch.randn(64, 4096, device="cuda").bfloat16()
+    d = _tc().gemm(a, b, 128, 64, 4096, False, False, out_dtype=torch.float32, splitk=8)
+    assert _rel(d, a.float() @ b.float().t()) < 1e-5
+
+
+CONVS = [(2, 64, 8, 8, 64, 1, 1, 0), (2, 64, 8, 8, 64, 3, 1, 1), (8, 64, 56, 56, 64, 3, 1, 1),
+         (8, 64, 56, 56, 128, 3, 2, 1), (8, 64, 56, 56, 128, 1, 2, 0), (8, 256, 14, 14, 256, 3, 1, 1),
+         (16, 512, 7, 7, 512, 3, 1, 1), (4, 64, 17, 17, 128, 3, 1, 0), (3, 128, 9, 11, 192, 5, 1, 2)]
+
+
+@pytest.mark.parametrize("n,c,h,w,k,r,stride,pad", CONVS)
+def test_conv_fprop_dgrad_wgrad(n, c, h, w, k, r, stride, pad):
+    tc = _tc()
+    torch.manual_seed(1)
+    x = torch.randn(n, c, h, w, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, c, r, r, device="cuda") * 0.1).bfloat16().contiguous(memory_format=torch.channels_last)
+    xf, wf = x.float().requires_grad_(True), wt.float().requires_grad_(True)
+    yref = F.conv2d(xf, wf, None, stride, pad)
+    gy = torch.randn_like(yref).bfloat16().contiguous(memory_format=torch.channels_last)
+    yref.backward(gy.float())
+    st, pd = (stride, stride), (pad, pad)
+    assert tc.fprop_ok(x, wt, st, pd, (1, 1), 1)
+    y, stats = tc.conv_fprop(x, wt, None, st, pd, True)
+    assert _rel(y, yref) < 8e-3                                 # bf16 output rounding
+    assert _rel(stats[:k], yref.sum(dim=(0, 2, 3))) < 1e-4      # stats come from the fp32 accumulator
+    assert _rel(stats[k:], (yref * yref).sum(dim=(0, 2, 3))) < 1e-4
+    if tc.dgrad_ok(x, wt, st, pd, (1, 1), 1):
+        assert _rel(tc.conv_dgrad(gy, wt, x.shape, st, pd), xf.grad) < 8e-3
+    else:
+        assert stride != 1
+    dw = tc.conv_wgrad(gy, x, wt.shape, st, pd)
+    assert dw.shape == wf.grad.shape and _rel(dw, wf.grad) < 2e-4
+    acc = torch.ones(k, r, r, c, device="cuda")                 # accumulate-into-arena form
+    tc.conv_wgrad(gy, x, wt.shape, st, pd, out=acc)
+    assert _rel(acc.permute(0, 3, 1, 2), wf.grad + 1.0) < 2e-4
+
+
+def test_resnet34_bf16_step_uses_tensor_core_kernels():
+    """bf16 ResNet-18 steps: native path (tcgen05 convs) tracks the torch/cuDNN autocast path."""
+    from mpi_pytorch_b200 import ops
+    from mpi_pytorch_b200.engine.trainer import Trainer
+    from mpi_pytorch_b200.parallel import bootstrap
+    from mpi_pytorch_b200.utils.config import Settings
+    w = bootstrap.init_world("cuda")
+    s = Settings(MODEL_NAME="resnet18", NUM_CLASSES=32, BATCH_SIZE=16, HEIGHT=64, WIDTH=64, USE_PRETRAINED=False,
+                 DTYPE="bf16", LR=1e-3)
+    losses = {}
+    before = _tc().LAUNCHES["n"]
+    for native in (True, False):
+        ops.set_native(native)
+        try:
+            tr = Trainer(s, w)
+            shard = tr.make_shard(total=64, shuffle=False)
+            losses[native] = [float(tr.train_step(x, y)) for x, y in shard]
+            tr.close()
+        finally:
+            ops.set_native(True)
+    assert _tc().LAUNCHES["n"] - before > 100                   # the convs really ran on the tcgen05 kernel
+    assert abs(losses[True][0] - losses[False][0]) < 0.05
+    assert losses[True][-1] < losses[True][0] + 0.5 and all(l == l for l in losses[True])
