@@ -1,0 +1,110 @@
+/* mpb200.h -- C ABI of libmpb200.so (mpi_pytorch_b200/lib/libmpb200.so), sm_100a only.
+ *
+ * Every function returns 0 on success, a cudaError_t value (> 0) when a CUDA call or launch failed,
+ * or a small negative number for an argument the kernel cannot handle (shape / alignment).
+ * Pointers are device pointers unless stated otherwise; `stream` is a cudaStream_t passed as void*.
+ * dtype: 0 = fp32, 1 = bf16.  4-D activations are NHWC (channels-last), C must be a multiple of 8.
+ * Citations point into the reference (/root/reference) at the call each entry point replaces.
+ */
+#ifndef MPB200_H_
+#define MPB200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- K10 softmax cross-entropy, fused forward+backward (main.py:134,150,152) ------------------------------
+ * loss_sum (1 float, zeroed inside) receives the MEAN loss; dlogits = (softmax - onehot)/B in logits' dtype. */
+int mpb_softmax_ce(const void* logits, const long long* target, void* dlogits, float* loss_sum, float* row_loss,
+                   int B, int C, int dtype, void* stream);
+/* argmax + compare + count (main.py:182-183, evaluation_pipeline.py:157-158); count is one int64, zeroed inside. */
+int mpb_count_correct(const void* logits, const long long* target, long long* count, int B, int C, int dtype,
+                      void* stream);
+
+/* ---- flat optimizers over an arena slice (main.py:155) ---------------------------------------------------- */
+int mpb_adam_flat(float* p, const float* g, float* m, float* v, void* shadow_bf16, long long n, int step, float lr,
+                  float b1, float b2, float eps, float wd, float grad_scale, void* stream);
+int mpb_sgd_flat(float* p, const float* g, float* buf, void* shadow_bf16, long long n, int step, float lr,
+                 float momentum, float wd, float grad_scale, void* stream);
+int mpb_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
+
+/* ---- K7 BatchNorm (+residual) (+ReLU), training and eval (torchvision BN layers built at models.py:33..87) -
+ * x is [M = N*H*W, C].  `sums` / `dsum` are 2*C floats of caller-provided scratch, zeroed inside.           */
+int mpb_bn_stats(const void* x, float* sums, long long M, int C, int dtype, void* stream);
+int mpb_bn_fwd_apply(const void* x, const void* res, void* out, const float* sums, const float* gamma,
+                     const float* beta, float* run_mean, float* run_var, float* save_mean, float* save_invstd,
+                     long long M, int C, float eps, float momentum, int relu, int training, int dtype, void* stream);
+int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float* gamma, const float* save_mean,
+               const float* save_invstd, float* dsum, void* dx, void* dres, float* dgamma, float* dbeta, long long M,
+               int C, int relu, int dtype, void* stream);
+
+/* ---- K8 pooling, K11 elementwise (ATen pooling / relu / dropout reached from models.py) ------------------- */
+int mpb_maxpool_fwd(const void* x, void* y, unsigned char* idx, int N, int H, int W, int C, int Ho, int Wo, int kh,
+                    int kw, int sh, int sw, int ph, int pw, int dtype, void* stream);
+int mpb_maxpool_bwd(const void* dy, const unsigned char* idx, void* dx, int N, int H, int W, int C, int Ho, int Wo,
+                    int kh, int kw, int sh, int sw, int ph, int pw, int dtype, void* stream);
+int mpb_avgpool(const void* in, void* out, int N, int H, int W, int C, int Ho, int Wo, int kh, int kw, int sh, int sw,
+                int ph, int pw, int count_include_pad, int backward, int dtype, void* stream);
+int mpb_adaptive_avgpool(const void* in, void* out, int N, int H, int W, int C, int Ho, int Wo, int backward,
+                         int dtype, void* stream);
+int mpb_relu_fwd(const void* x, void* y, long long n, int dtype, void* stream);
+int mpb_relu_bwd(const void* dy, const void* y, void* dx, long long n, int dtype, void* stream);
+int mpb_dropout(const void* x, void* y, long long n, unsigned int seed, float p, int dtype, void* stream);
+
+/* ---- K9 resize + normalise, K14 synthetic data (main.py:62-65, evaluation_pipeline.py:89,116-122) ---------
+ * mode 0: u8 -> u8 NHWC; 1: u8 -> normalised float via a u8 rounding (PIL semantics); 2: u8 -> float directly. */
+int mpb_resize(const unsigned char* in, void* out, int N, int Hi, int Wi, int Ho, int Wo, int bicubic, int mode,
+               int out_nhwc, int out_dtype, void* stream);
+int mpb_normalize_u8(const unsigned char* in, void* out, int N, int H, int W, int out_nhwc, int out_dtype,
+                     void* stream);
+int mpb_synth_images(void* out, const long long* index, int n, int C, int H, int W, long long seed, int out_nhwc,
+                     int out_dtype, void* stream);
+
+/* ---- K3-K6 tcgen05 / TMEM / TMA GEMM and implicit-GEMM convolution (every nn.Conv2d / nn.Linear) ----------
+ * bf16 operands, fp32 accumulation.  GEMM: D[M,N] = A[M,K] * B[N,K]^T with either operand K-major
+ * ([rows][K]) or MN-major ([K][rows]).  out_mode 0: bf16, 1: fp32, 2: fp32 atomic accumulate (split-K).     */
+int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias, int M, int N, int K, long long lda,
+                long long ldb, long long ldd, int a_mn, int b_mn, int out_mode, int splitk, void* stream);
+/* y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C]); C % 64 == 0, K % 16 == 0.  stats: optional 2*K floats, zeroed by the
+ * caller, receive per-channel sum / sum of squares of the fp32 accumulator (BatchNorm statistics).            */
+int mpb_tc_conv_fprop(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H, int W,
+                      int C, int K, int R, int S, int P, int Q, int stride, int pad_h, int pad_w, int dil,
+                      void* stream);
+/* dx for stride-1 convolutions; the filter is read in place as an MN-major operand (no transposed copy).      */
+int mpb_tc_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int K, int R, int S, int P,
+                      int Q, int pad_h, int pad_w, void* stream);
+/* dw[K,R,S,C] (fp32) += split-K partial sums; dw must hold zeros or a partial gradient to accumulate into.     */
+int mpb_tc_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R, int S,
+                      int P, int Q, int stride, int pad_h, int pad_w, int dil, int splitk, void* stream);
+
+/* ---- K1 / K2 / K13 peer-memory collectives over NVLink (mpi_tools.py:30-37,47-53; evaluation_pipeline.py:196)
+ * Symmetric buffers: cudaMalloc on every rank, handles exchanged by the caller, mapped with the ipc helpers.
+ * `grads/params/shadows/pads/bufs/vals` are HOST arrays of W device pointers indexed by rank, already offset
+ * to the range being reduced.  `epochs` is this rank's private device array of mpb_epoch_bytes() bytes.       */
+int mpb_sym_alloc(void** ptr, long long bytes);
+int mpb_sym_free(void* ptr);
+int mpb_ipc_get_handle(void* ptr, void* handle_out64);
+int mpb_ipc_open_handle(const void* handle64, void** ptr);
+int mpb_ipc_close_handle(void* ptr);
+int mpb_ipc_handle_bytes(void);
+int mpb_signal_pad_bytes(void);
+int mpb_epoch_bytes(void);
+long long mpb_oneshot_max_elems(int blocks);
+/* algo 0 one-shot, 1 two-shot.  opt_kind 0: grads averaged in place; 1 Adam / 2 SGD-momentum: fp32 params and
+ * optional bf16 shadows updated on every rank from the averaged gradient (two-shot: owner slice + all-gather).
+ * step_dev: optional device int holding the optimizer step (used instead of `step` when non-null).            */
+int mpb_allreduce_fused(void* const* grads, void* const* params, void* const* shadows, void* const* pads,
+                        void* epochs, float* m, float* v, long long n, int rank, int W, int algo, int blocks,
+                        int opt_kind, int step, float lr, float b1, float b2, float eps, float wd, float momentum,
+                        const int* step_dev, void* stream);
+int mpb_broadcast(void* const* bufs, void* const* pads, void* epochs, long long n_floats, int rank, int W, int root,
+                  int blocks, void* stream);
+int mpb_allgather_slices(void* const* bufs, void* const* pads, void* epochs, long long n_floats, int rank, int W,
+                         int blocks, void* stream);
+int mpb_count_allreduce(void* const* vals, void* const* pads, void* epochs, long long* out, int rank, int W,
+                        void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPB200_H_ */

@@ -35,6 +35,7 @@ struct OptArgs {
   int kind;           // 0 = none (write averaged grads), 1 = adam, 2 = sgd-momentum
   float lr, b1, b2, eps, wd, bc1, bc2_sqrt, momentum;
   int first_step;
+  const int* step_ptr;  // optional device-resident step counter (CUDA-graph replays: bias corrections follow it)
 };
 
 namespace {
@@ -113,6 +114,12 @@ __device__ __forceinline__ float4 sum_peers(const ArParams& P, long long i4) {
 
 template <int W>
 __global__ void __launch_bounds__(MPB_COMM_THREADS, 1) allreduce_kernel(ArParams P) {
+  if (P.opt.kind != 0 && P.opt.step_ptr != nullptr) {
+    const int step = *P.opt.step_ptr;
+    P.opt.first_step = (step == 1);
+    P.opt.bc1 = 1.f - powf(P.opt.b1, (float)step);
+    P.opt.bc2_sqrt = sqrtf(1.f - powf(P.opt.b2, (float)step));
+  }
   const uint32_t e0 = P.epochs[blockIdx.x];
   rank_barrier(P.pads, P.rank, W, e0 + 1);            // every peer's gradients are complete and visible
   const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -292,7 +299,7 @@ MPB_API long long mpb_oneshot_max_elems(int blocks) { return (long long)blocks *
 MPB_API int mpb_allreduce_fused(void* const* grads, void* const* params, void* const* shadows, void* const* pads,
                                 void* epochs, float* m, float* v, long long n, int rank, int W, int algo, int blocks,
                                 int opt_kind, int step, float lr, float b1, float b2, float eps, float wd,
-                                float momentum, void* stream) {
+                                float momentum, const int* step_dev, void* stream) {
   if (W < 1 || W > MPB_MAX_WORLD || n <= 0 || (n % (4 * W)) != 0) return -1;
   if (blocks < 1) blocks = 1;
   if (blocks > MPB_MAX_COMM_BLOCKS) blocks = MPB_MAX_COMM_BLOCKS;
@@ -308,7 +315,7 @@ MPB_API int mpb_allreduce_fused(void* const* grads, void* const* params, void* c
   P.epochs = (uint32_t*)epochs; P.m = m; P.v = v; P.n = n; P.rank = rank; P.W = W; P.algo = algo;
   P.scale = 1.f / (float)W;
   P.opt.kind = opt_kind; P.opt.lr = lr; P.opt.b1 = b1; P.opt.b2 = b2; P.opt.eps = eps; P.opt.wd = wd;
-  P.opt.momentum = momentum; P.opt.first_step = (step == 1);
+  P.opt.momentum = momentum; P.opt.first_step = (step == 1); P.opt.step_ptr = step_dev;
   P.opt.bc1 = 1.f - powf(b1, (float)step);
   P.opt.bc2_sqrt = sqrtf(1.f - powf(b2, (float)step));
   cudaStream_t st = (cudaStream_t)stream;

@@ -50,6 +50,15 @@ def loss_from_outputs(outputs: Any, labels: torch.Tensor) -> torch.Tensor:
     return ops.cross_entropy(outputs, labels)
 
 
+def count_launches(engine) -> int:
+    """Kernels of this framework launched so far (ops + tensor-core + peer collectives)."""
+    n = int(getattr(engine.coll, "launches", 0))
+    if engine.device.type == "cuda" and ops.native_enabled():
+        from ..ops import tc
+        n += ops.native().LAUNCHES["n"] + tc.LAUNCHES["n"]
+    return n
+
+
 class Trainer:
     """One model replica + its DP engine.  ``train_step`` is the hot loop body of main.py:146-156."""
 
@@ -77,6 +86,9 @@ class Trainer:
         self.optimizer = self.engine.optimizer
         self.start_epoch = 0
         self.autocast = (self.dtype == torch.bfloat16 and not ops.native_enabled())
+        self._graph = None
+        self._graph_static = None
+        self.graph_launches_per_step = 0
 
     # ------------------------------------------------------------------ set-up helpers
     def maybe_resume(self) -> None:
@@ -116,6 +128,43 @@ class Trainer:
         loss.backward()
         self.optimizer.step()
         return loss.detach()
+
+    # ------------------------------------------------------------------ CUDA-graph replay of the whole step
+    def graph_capable(self) -> bool:
+        """Whole-step capture needs a CUDA device, fixed shapes and no host-seeded randomness (Dropout)."""
+        if self.device.type != "cuda":
+            return False
+        return not any(isinstance(m, nn.Dropout) and m.p > 0 for m in self.model.modules())
+
+    def train_step_graphed(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """Same work as :meth:`train_step`, but forward + backward + bucketed all-reduce + fused Adam are
+        captured once into a CUDA graph and replayed: one host call per step instead of ~600 launches
+        (the eager step is host-bound on B200: ~18 ms of Python/launch overhead vs ~17 ms of kernels)."""
+        if self._graph is None:
+            self._capture(images, labels)
+        sx, sy, sloss = self._graph_static
+        sx.copy_(images, non_blocking=True)
+        sy.copy_(labels, non_blocking=True)
+        self._graph.replay()
+        self.engine.step_count += 1
+        return sloss
+
+    def _capture(self, images: torch.Tensor, labels: torch.Tensor) -> None:
+        sx, sy = images.clone(), labels.clone()
+        cur = torch.cuda.current_stream(self.device)
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for _ in range(2):                       # warm-up on a side stream (real optimizer steps)
+                self.train_step(sx, sy)
+        cur.wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        n0 = count_launches(self.engine)
+        with torch.cuda.graph(g):
+            sloss = self.train_step(sx, sy)
+        self.graph_launches_per_step = count_launches(self.engine) - n0     # our kernels inside one replay
+        self._graph, self._graph_static = g, (sx, sy, sloss)
 
     @torch.no_grad()
     def evaluate(self, shard: SyntheticShard) -> float:

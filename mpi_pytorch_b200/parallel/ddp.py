@@ -76,7 +76,7 @@ class FusedOptimizer(torch.optim.Optimizer):
                     eng.layout.view(eng.state[key], p).copy_(st[key].to(eng.state[key].dtype).reshape(p.shape))
             if "step" in st:
                 step = max(step, int(float(st["step"])))
-        eng.step_count = step
+        eng.set_step(step)
         g0 = groups[0]
         self.param_groups[0]["lr"] = g0.get("lr", self.param_groups[0]["lr"])
         self._hyper.lr = float(self.param_groups[0]["lr"])
@@ -115,6 +115,12 @@ class FusedDataParallel:
         keys = ("exp_avg", "exp_avg_sq") if self.hyper.kind == "adam" else ("momentum_buffer",)
         self.state = {k: torch.zeros(max(n, 1), dtype=torch.float32, device=dev) for k in keys}
         self.step_count = 0
+        # device-resident mirror of the optimizer step: the fused kernels read it, so a captured CUDA graph
+        # keeps applying the right Adam bias corrections on every replay
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev) if dev.type == "cuda" else None
+        self._step_advanced = False
+        if hasattr(self.coll, "step_dev"):
+            self.coll.step_dev = self.step_dev
         self._rebind_parameters()
         for b in self.layout.buckets:
             b.algo = algo
@@ -182,6 +188,9 @@ class FusedDataParallel:
     def zero_grad(self) -> None:
         self.grad_arena.zero_()
         self._reset_pending()
+        if self.step_dev is not None and not self._step_advanced:
+            self.step_dev.add_(1)                 # once per optimizer step, before any bucket launches
+            self._step_advanced = True
 
     def _launch(self, b: Bucket) -> None:
         g = self.layout.bucket_view(self.grad_arena, b)
@@ -215,7 +224,13 @@ class FusedDataParallel:
         if self.comm_stream is not None and self.overlap:
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
         self.step_count += 1
+        self._step_advanced = False
         self._reset_pending()
+
+    def set_step(self, step: int) -> None:
+        self.step_count = int(step)
+        if self.step_dev is not None:
+            self.step_dev.fill_(int(step))
 
     @torch.no_grad()
     def average_gradients_only(self) -> None:

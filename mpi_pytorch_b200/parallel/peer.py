@@ -54,6 +54,7 @@ class PeerCollectives:
         self.comm_blocks = comm_blocks
         self.bufs: List[_SymBuf] = []
         self.launches = 0
+        self.step_dev: Optional[torch.Tensor] = None    # device-resident optimizer step (set by the DP engine)
         torch.cuda.set_device(self.device)
         pad_bytes = self.lib.mpb_signal_pad_bytes()
         self.pad = self._sym_alloc(pad_bytes)
@@ -150,7 +151,8 @@ class PeerCollectives:
             c_void_p(0 if m is None else m.data_ptr()), c_void_p(0 if v is None else v.data_ptr()),
             c_ll(n), c_int(self.rank), c_int(self.size), c_int(a), c_int(blocks), c_int(kind), c_int(step),
             c_float(h.lr), c_float(h.beta1), c_float(h.beta2), c_float(h.eps), c_float(h.weight_decay),
-            c_float(h.momentum), c_void_p(torch.cuda.current_stream().cuda_stream))
+            c_float(h.momentum), c_void_p(0 if self.step_dev is None else self.step_dev.data_ptr()),
+            c_void_p(torch.cuda.current_stream().cuda_stream))
         self.launches += 1
         if rc != 0:
             raise RuntimeError("mpb_allreduce_fused failed: {}".format(rc))
