@@ -140,7 +140,13 @@ def conv_wgrad(gy, x, w_shape, stride, padding, out: Optional[torch.Tensor] = No
     bn = 128 if c % 128 == 0 else 64
     tiles = ((k + 127) // 128) * r * s * (c // bn)
     num_kb = (n * p * q + 63) // 64
-    splitk = max(1, min((SMS * 6 + tiles - 1) // tiles, max(1, num_kb // 4)))
+    # split-K: enough CTAs to fill the machine (>= 2 per SM) but >= ~96 K-blocks each, so the fp32 atomic
+    # epilogue (128 x BN RED ops per CTA) stays a small fraction of the CTA's life (measured sweep)
+    lo, hi = (2 * SMS + tiles - 1) // tiles, (8 * SMS + tiles - 1) // tiles
+    splitk = max(1, min(hi, max(lo, num_kb // 96)))
+    if "MPB_WGRAD_CTAS" in os.environ:
+        splitk = max(1, (int(os.environ["MPB_WGRAD_CTAS"]) + tiles - 1) // tiles)
+    splitk = min(splitk, max(1, num_kb))
     rc = _LIB.mpb_tc_conv_wgrad(_p(gy), _p(x), _p(dw), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r),
                                 c_int(s), c_int(p), c_int(q), c_int(stride[0]), c_int(padding[0]), c_int(padding[1]),
                                 c_int(1), c_int(splitk), c_void_p(_stream()))
