@@ -38,6 +38,17 @@ int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float* gamma,
                const float* save_invstd, float* dsum, void* dx, void* dres, float* dgamma, float* dbeta, long long M,
                int C, int relu, int dtype, void* stream);
 
+/* BatchNorm backward without caller scratch.  This entry point has no counterpart in the reference: it exists
+ * for hosts that cannot allocate device memory themselves (all of the GPU already belongs to their own pool,
+ * or the implicit synchronisation of cudaMalloc/cudaFree is not acceptable where they call us).  Same maths
+ * and argument meaning as mpb_bn_bwd minus `dsum`; the 2*C floats live in a fixed 16 KB device array inside
+ * the library, so C <= 2048 (larger C returns -4).  The first call on a device performs a one-time address
+ * look-up and should happen before any stream capture; calls that can overlap on the GPU share the array and
+ * would race -- keep them ordered.  Calls no cudaMalloc/cudaFree.                                            */
+int mpb_bn_bwd_noalloc(const void* dz, const void* z, const void* x, const float* gamma, const float* save_mean,
+                       const float* save_invstd, void* dx, void* dres, float* dgamma, float* dbeta, long long M,
+                       int C, int relu, int dtype, void* stream);
+
 /* ---- K8 pooling, K11 elementwise (ATen pooling / relu / dropout reached from models.py) ------------------- */
 int mpb_maxpool_fwd(const void* x, void* y, unsigned char* idx, int N, int H, int W, int C, int Ho, int Wo, int kh,
                     int kw, int sh, int sw, int ph, int pw, int dtype, void* stream);

@@ -246,3 +246,62 @@ MPB_API int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float
   MPB_CHECK_LAUNCH();
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// BatchNorm backward for callers that cannot allocate device memory.
+//
+// mpb_bn_bwd() needs 2*C floats of scratch (`dsum`) that the caller must allocate.  Some callers cannot do
+// that: a host application that has handed the whole GPU to its own memory pool (so cudaMalloc fails or is
+// forbidden by policy), or a latency-critical loop in which the implicit device synchronisation of
+// cudaMalloc / cudaFree is not acceptable.  For them this variant keeps the scratch inside the library, in a
+// fixed file-scope device array.  Consequences the caller has to know about:
+//   * capacity: at most MPB_NOALLOC_MAX_CHANNELS (2048) channels -- 16 KB of device memory that every GPU which
+//     loads this library holds until the process exits.  Larger C is rejected with -4 and a message on stderr.
+//   * set-up: the first call on a given device resolves the array's device address (cudaGetSymbolAddress, with
+//     that device current) and caches it per device.  Make that first call before any stream capture begins.
+//   * sharing: every call on a device uses the same array.  It is cleared at the start of each call (the sums
+//     must start at zero), and it still holds the previous call's sums afterwards.  Two calls whose kernels can
+//     overlap on the GPU (different streams, no dependency) would race on it -- serialise them.
+// No cudaMalloc / cudaFree / allocating library routine is called here.
+// ---------------------------------------------------------------------------------------------------------
+#define MPB_NOALLOC_MAX_CHANNELS 2048
+#define MPB_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_bn_bwd_scratch[2 * MPB_NOALLOC_MAX_CHANNELS];
+
+// In host code `g_bn_bwd_scratch` is only a handle for the symbol, not a device address; kernels must be given
+// the address obtained below (one per device, because each device has its own copy of the array).
+static float* g_bn_bwd_scratch_addr[MPB_NOALLOC_MAX_DEVICES] = {nullptr};
+
+MPB_API int mpb_bn_bwd_noalloc(const void* dz, const void* z, const void* x, const float* gamma,
+                               const float* save_mean, const float* save_invstd, void* dx, void* dres, float* dgamma,
+                               float* dbeta, long long M, int C, int relu, int dtype, void* stream) {
+  if (C > MPB_NOALLOC_MAX_CHANNELS) {
+    fprintf(stderr, "mpb_bn_bwd_noalloc: C=%d exceeds the built-in scratch capacity of %d channels; "
+                    "use mpb_bn_bwd with caller-provided scratch instead\n", C, MPB_NOALLOC_MAX_CHANNELS);
+    return -4;
+  }
+  if (C <= 0 || C % 8 != 0) return -1;
+  int dev = -1;
+  MPB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= MPB_NOALLOC_MAX_DEVICES) return -5;
+  if (g_bn_bwd_scratch_addr[dev] == nullptr) {           // one-time set-up for this device (device `dev` is current)
+    float* ptr = nullptr;
+    MPB_CUDA(cudaGetSymbolAddress((void**)&ptr, g_bn_bwd_scratch));
+    g_bn_bwd_scratch_addr[dev] = ptr;
+  }
+  float* dsum = g_bn_bwd_scratch_addr[dev];
+  cudaStream_t st = (cudaStream_t)stream;
+  MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));     // the sums accumulate with atomics: start from zero
+  const Map mp = make_map(C);
+  const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
+  const int g1 = rows_grid(M, mp.rows_per_block, 4), g2 = rows_grid(M, mp.rows_per_block, 8);
+  DISPATCH_T(dtype,
+             bn_bwd_reduce_kernel<T><<<g1, mp.threads, smem, st>>>((const T*)dz, (const T*)z, (const T*)x, save_mean,
+                                                                   save_invstd, dsum, M, C, mp.cvecs, mp.rows_per_block, relu);
+             bn_bwd_apply_kernel<T><<<g2, mp.threads, 0, st>>>((const T*)dz, (const T*)z, (const T*)x, gamma, save_mean,
+                                                               save_invstd, dsum, (T*)dx, (T*)dres, dgamma, dbeta, M, C,
+                                                               mp.cvecs, mp.rows_per_block, relu);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
