@@ -110,3 +110,79 @@ def create_dataset(train_dir: str, train_file: str, n_images: int, out_dir: str 
                 os.makedirs(os.path.dirname(dst), exist_ok=True)
                 shutil.copy2(os.path.join(train_dir, src), dst)
     return p_tr, p_te
+
+
+class FileShard:
+    """This rank's slice of a CSV-indexed JPEG dataset, batched for the GPU.
+
+    The reference decodes, resizes and normalises every sample on the CPU inside a 0-worker
+    DataLoader (main.py:62-65,102; data_loader.py:29-37).  Here the CPU only decodes to uint8; each
+    frame is uploaded as-is and resized + normalised on the device by the fused ``ops.resize_normalize``
+    kernel (train-time semantics: antialiased bilinear on the float image, then ImageNet mean/std)."""
+
+    def __init__(self, directory: str, frame, batch_size: int, hw: Tuple[int, int], rank: int = 0, world: int = 1,
+                 device="cpu", dtype: torch.dtype = torch.float32, channels_last: bool = False, shuffle: bool = True,
+                 seed: int = 0, mode: str = "train"):
+        rows = shard_rows(len(frame), rank, world, equalize=True)
+        part = frame.iloc[rows]
+        self.ds = GetData(directory, part["file_name"].values, part["category_id"].values, None, mode=mode)
+        self.batch_size, self.hw, self.device = int(batch_size), hw, torch.device(device)
+        self.dtype, self.channels_last, self.shuffle, self.seed, self.rank = dtype, channels_last, shuffle, seed, rank
+        self.total = len(frame)
+        self.epoch = 0
+
+    def __len__(self) -> int:
+        return (len(self.ds) + self.batch_size - 1) // self.batch_size
+
+    @property
+    def num_samples(self) -> int:
+        return len(self.ds)
+
+    def set_epoch(self, epoch: int) -> None:
+        self.epoch = int(epoch)
+
+    def __iter__(self):
+        from .. import ops
+        n = len(self.ds)
+        order = torch.arange(n)
+        if self.shuffle:
+            g = torch.Generator().manual_seed(self.seed * 1000003 + self.epoch * 7919 + self.rank)
+            order = torch.randperm(n, generator=g)
+        for b in range(len(self)):
+            idx = order[b * self.batch_size:(b + 1) * self.batch_size].tolist()
+            frames = [self.ds.load_uint8(i) for i in idx]
+            labels = torch.as_tensor([int(self.ds.labels[i]) for i in idx], dtype=torch.int64)
+            outs = []
+            for f in frames:                           # one launch per distinct frame size (Herbarium: ~1000x680 for all)
+                u8 = f.unsqueeze(0).to(self.device, non_blocking=True)
+                outs.append(ops.resize_normalize(u8, self.hw[0], self.hw[1], "bilinear", self.dtype, self.channels_last))
+            x = torch.cat(outs, dim=0)
+            if self.channels_last:
+                x = x.contiguous(memory_format=torch.channels_last)
+            yield x, labels.to(self.device)
+
+
+def make_synthetic_index(out_dir: str, n_train: int = 64, n_test: int = 16, num_classes: int = 10, hw=(40, 28),
+                         seed: int = 0):
+    """Write a tiny Herbarium-shaped dataset (JPEG files + the two CSV indices with the reference's columns,
+    data/*.csv:1) so the file-backed path can be exercised without the 6 GB original."""
+    import pandas as pd
+    from PIL import Image
+    rng = np.random.RandomState(seed)
+    paths = {}
+    for split, n in (("train", n_train), ("test", n_test)):
+        rows = []
+        for i in range(n):
+            cat = int(rng.randint(0, num_classes))
+            rel = "images/{:03d}/{:02d}/{}.jpg".format(cat, i % 100, 100000 + i)
+            full = os.path.join(out_dir, split, rel)
+            os.makedirs(os.path.dirname(full), exist_ok=True)
+            arr = (rng.rand(hw[0], hw[1], 3) * 255).astype(np.uint8)
+            arr[:, :, cat % 3] = np.clip(arr[:, :, cat % 3].astype(int) + 20 * cat, 0, 255).astype(np.uint8)
+            Image.fromarray(arr).save(full, quality=95)
+            rows.append({"file_name": rel, "height": hw[0], "id": 100000 + i, "license": 0, "width": hw[1],
+                         "category_id": cat, "institution_id": 0})
+        df = pd.DataFrame(rows, columns=CSV_COLUMNS)
+        paths[split] = os.path.join(out_dir, "{}_sample.csv".format(split))
+        df.to_csv(paths[split])
+    return paths["train"], paths["test"]

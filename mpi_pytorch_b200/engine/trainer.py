@@ -102,6 +102,19 @@ class Trainer:
     def sync_params(self) -> None:
         self.engine.sync_params(0)
 
+    def make_file_shards(self):
+        """CSV + JPEG path (SYNTHETIC=False): rank-local training shard and, on rank 0, the un-sharded
+        validation set -- the same split logic as main.py:73-112, minus the pickled scatter."""
+        from ..data.dataset import FileShard, load_index
+        train_df, _ = load_index(self.s.TRAIN_CSV, self.s.TEST_CSV, self.s.DEBUG, self.s.SEED)
+        tr = FileShard(self.s.TRAIN_DIR, train_df, self.s.BATCH_SIZE, self.hw, self.world.rank, self.world.size,
+                       self.device, self.dtype, self.channels_last, True, self.s.SEED, mode="train")
+        va = None
+        if self.s.VALIDATE and self.world.rank == 0:
+            va = FileShard(self.s.TRAIN_DIR, train_df, self.s.BATCH_SIZE, self.hw, 0, 1, self.device, self.dtype,
+                           self.channels_last, False, self.s.SEED, mode="train")
+        return tr, va
+
     def make_shard(self, total: Optional[int] = None, shuffle: bool = True, all_ranks: bool = True) -> SyntheticShard:
         if total is None:
             total = self.s.SYNTHETIC_SAMPLES or (800 if self.s.DEBUG else 40000)   # main.py:73-82 sizes
@@ -187,6 +200,8 @@ class Trainer:
     def fit(self, train: Optional[SyntheticShard] = None, val: Optional[SyntheticShard] = None,
             epochs: Optional[int] = None) -> List[Dict[str, float]]:
         s, log, w = self.s, self.log, self.world
+        if train is None and not s.SYNTHETIC:
+            train, val = self.make_file_shards()
         train = train or self.make_shard()
         log.info("_Files Received: {}".format(train.num_samples))
         if val is None and s.VALIDATE and w.rank == 0:

@@ -1,0 +1,59 @@
+"""Loss-curve equivalence against the UNMODIFIED reference (SURVEY §4 test plan).
+
+A subprocess imports /root/reference/{models,mpi_tools}.py behind the gloo-backed mpi4py stand-in
+(baseline/mpi4py_shim) and runs the reference's step order (main.py:146-156) for a few steps on fixed
+tensors; our Trainer runs the same steps on CPU fp32 from the same seed.  Same seed -> same torchvision-order
+initialisation -> the two loss curves must agree to fp tolerance."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = "/root/reference" if os.path.exists("/root/reference/mpi_tools.py") else os.path.join(ROOT, "baseline", "_ref")
+
+_SCRIPT = r'''
+import sys, json, torch
+sys.path[:0] = [%(shim)r, %(ref)r]
+import models, mpi_tools, utils
+torch.set_num_threads(1)
+torch.manual_seed(0)
+model, _ = models.initialize_model("resnet18", 10, False, use_pretrained=False)
+opt = torch.optim.Adam(model.parameters(), lr=utils.LR)
+mpi_tools.sync_params(model)
+crit = torch.nn.CrossEntropyLoss()
+g = torch.Generator().manual_seed(42)
+X = torch.randn(3, 4, 3, 32, 32, generator=g); Y = torch.randint(0, 10, (3, 4), generator=g)
+losses = []
+model.train()
+for s in range(3):
+    logits = model(X[s].float()); loss = crit(logits, Y[s])
+    opt.zero_grad(); loss.backward(); mpi_tools.mpi_avg_grads(model); opt.step()
+    losses.append(loss.item())
+print(json.dumps(losses))
+'''
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(REF, "mpi_tools.py")), reason="reference sources not available")
+def test_loss_curve_matches_reference_loop():
+    import warnings
+    code = _SCRIPT % {"shim": os.path.join(ROOT, "baseline", "mpi4py_shim"), "ref": REF}
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    out = subprocess.run([sys.executable, "-W", "ignore", "-c", code], capture_output=True, text=True, env=env, cwd="/tmp")
+    assert out.returncode == 0, out.stderr[-2000:]
+    ref_losses = json.loads(out.stdout.strip().splitlines()[-1])
+
+    from mpi_pytorch_b200.engine.trainer import Trainer
+    from mpi_pytorch_b200.utils.config import Settings
+    s = Settings(MODEL_NAME="resnet18", NUM_CLASSES=10, BATCH_SIZE=4, HEIGHT=32, WIDTH=32, USE_PRETRAINED=False,
+                 DEVICE="cpu", DTYPE="fp32", LR=4e-4, SEED=0)
+    tr = Trainer(s)
+    g = torch.Generator().manual_seed(42)
+    X = torch.randn(3, 4, 3, 32, 32, generator=g)
+    Y = torch.randint(0, 10, (3, 4), generator=g)
+    mine = [float(tr.train_step(X[i], Y[i])) for i in range(3)]
+    for a, b in zip(mine, ref_losses):
+        assert abs(a - b) < 2e-4 * max(1.0, abs(b)), (mine, ref_losses)
