@@ -93,16 +93,17 @@ def _base_ok(x, w, stride, padding, dilation, groups) -> bool:
 
 
 def fprop_ok(x, w, stride, padding, dilation, groups) -> bool:
-    return _base_ok(x, w, stride, padding, dilation, groups) and x.shape[1] % 64 == 0 and w.shape[0] % 16 == 0
+    # channel tails are handled by TMA out-of-bounds zero fill; 16-byte global strides need C, K multiples of 8
+    return _base_ok(x, w, stride, padding, dilation, groups) and x.shape[1] % 8 == 0 and w.shape[0] % 8 == 0
 
 
 def dgrad_ok(x, w, stride, padding, dilation, groups) -> bool:
-    return (_base_ok(x, w, stride, padding, dilation, groups) and stride[0] == 1 and x.shape[1] % 64 == 0
-            and w.shape[0] % 64 == 0 and padding[0] <= w.shape[2] - 1 and padding[1] <= w.shape[3] - 1)
+    return (_base_ok(x, w, stride, padding, dilation, groups) and stride[0] == 1 and x.shape[1] % 8 == 0
+            and w.shape[0] % 8 == 0 and padding[0] <= w.shape[2] - 1 and padding[1] <= w.shape[3] - 1)
 
 
 def wgrad_ok(x, w, stride, padding, dilation, groups) -> bool:
-    return _base_ok(x, w, stride, padding, dilation, groups) and x.shape[1] % 64 == 0 and w.shape[0] % 8 == 0
+    return _base_ok(x, w, stride, padding, dilation, groups) and x.shape[1] % 8 == 0 and w.shape[0] % 8 == 0
 
 
 def conv_supported(x, w, stride, padding, dilation, groups) -> bool:
@@ -137,8 +138,8 @@ def conv_wgrad(gy, x, w_shape, stride, padding, out: Optional[torch.Tensor] = No
     atomically accumulated straight into it -- no temporary, no separate add."""
     n, c, h, wd, k, r, s, p, q = _geom(x.shape, w_shape, stride, padding)
     dw = torch.zeros((k, r, s, c), dtype=torch.float32, device=gy.device) if out is None else out
-    bn = 128 if c % 128 == 0 else 64
-    tiles = ((k + 127) // 128) * r * s * (c // bn)
+    bn = 128 if c > 64 else 64
+    tiles = ((k + 127) // 128) * r * s * ((c + bn - 1) // bn)
     num_kb = (n * p * q + 63) // 64
     # split-K: enough CTAs to fill the machine (>= 2 per SM) but >= ~96 K-blocks each, so the fp32 atomic
     # epilogue (128 x BN RED ops per CTA) stays a small fraction of the CTA's life (measured sweep, DESIGN.md)

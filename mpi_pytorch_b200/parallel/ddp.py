@@ -157,6 +157,7 @@ class FusedDataParallel:
     def _reset_pending(self) -> None:
         for b in self.layout.buckets:
             b.pending = len(b.params)
+        self._fired = set()
         self._in_flight = []
 
     # ------------------------------------------------------------------ weight sync (C14 / K2)
@@ -209,6 +210,11 @@ class FusedDataParallel:
         self._in_flight.append(b)
 
     def _on_grad(self, p: nn.Parameter) -> None:
+        # Idempotent per step: a kernel that wrote p.grad in place reports completion explicitly, and autograd may
+        # additionally run the post-accumulate hook for the same parameter (observed on B200 / torch 2.11).
+        if id(p) in self._fired:
+            return
+        self._fired.add(id(p))
         b = self.layout.buckets[self.layout.slots[id(p)].bucket]
         b.pending -= 1
         if b.pending == 0:
