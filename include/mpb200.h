@@ -74,8 +74,12 @@ int mpb_synth_images(void* out, const long long* index, int n, int C, int H, int
 /* ---- K3-K6 tcgen05 / TMEM / TMA GEMM and implicit-GEMM convolution (every nn.Conv2d / nn.Linear) ----------
  * bf16 operands, fp32 accumulation.  GEMM: D[M,N] = A[M,K] * B[N,K]^T with either operand K-major
  * ([rows][K]) or MN-major ([K][rows]).  out_mode 0: bf16, 1: fp32, 2: fp32 atomic accumulate (split-K).     */
-int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias, int M, int N, int K, long long lda,
-                long long ldb, long long ldd, int a_mn, int b_mn, int out_mode, int splitk, void* stream);
+int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias, float* stats, int M, int N, int K,
+                long long lda, long long ldb, long long ldd, int a_mn, int b_mn, int out_mode, int splitk, void* stream);
+/* explicit im2col (rows = output pixels, columns = (r,s,c) zero-padded to Kpad) for inputs whose channel count is
+ * not a multiple of 8 (3-channel stems); feeds mpb_tc_gemm for fprop and wgrad.                               */
+int mpb_im2col_nhwc(const void* x, void* out, int N, int H, int W, int C, int R, int S, int P, int Q, int stride,
+                    int pad_h, int pad_w, int Kpad, void* stream);
 /* y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C]); C % 64 == 0, K % 16 == 0.  stats: optional 2*K floats, zeroed by the
  * caller, receive per-channel sum / sum of squares of the fp32 accumulator (BatchNorm statistics).            */
 int mpb_tc_conv_fprop(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H, int W,

@@ -459,8 +459,10 @@ int pick_bn(int n) {
 //   a_mn = 0: A stored [M][K] (row stride lda)      a_mn = 1: A stored [K][M] (row stride lda)
 //   b_mn = 0: B stored [N][K] (row stride ldb)      b_mn = 1: B stored [K][N] (row stride ldb)
 //   out_mode 0: bf16 D, 1: fp32 D, 2: fp32 atomic accumulate with split-K (D must be pre-zeroed)
-MPB_API int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias, int M, int N, int K, long long lda,
-                        long long ldb, long long ldd, int a_mn, int b_mn, int out_mode, int splitk, void* stream) {
+//   stats (optional, no split-K): 2*N floats zeroed by the caller, receive per-column sum / sum of squares of D
+MPB_API int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias, float* stats, int M, int N, int K,
+                        long long lda, long long ldb, long long ldd, int a_mn, int b_mn, int out_mode, int splitk,
+                        void* stream) {
   int rc = load_driver_fns();
   if (rc) return rc;
   if (M <= 0 || N <= 0 || K <= 0) return 0;
@@ -474,7 +476,7 @@ MPB_API int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias
   if (out_mode != OUT_ATOMIC_F32) splitk = 1;
   p.kb_per_split = (p.num_kb + splitk - 1) / splitk;
   p.idesc = make_idesc(p.BN, a_mn, b_mn);
-  p.out_mode = out_mode; p.D = D; p.ldd = ldd; p.bias = bias;
+  p.out_mode = out_mode; p.D = D; p.ldd = ldd; p.bias = bias; p.stats = (splitk == 1) ? stats : nullptr;
   CUtensorMap ta, tb;
   rc = a_mn ? make_map_2d(&ta, A, K, M, lda, 64, 64) : make_map_2d(&ta, A, M, K, lda, 64, BM);
   if (rc) return rc;
@@ -557,4 +559,59 @@ MPB_API int mpb_tc_conv_wgrad(const void* dy, const void* x, float* dw, int N, i
   if (rc) return rc - 1000;
   dim3 grid((K + BM - 1) / BM, R * S * p.tap_cols, (p.num_kb + p.kb_per_split - 1) / p.kb_per_split);
   return launch(ta, tb, p, grid, (cudaStream_t)stream);
+}
+
+
+// ------------------------------------------------------------------------------------------------------------
+// Explicit im2col for convolutions whose input channel count is not a multiple of 8 (the 3-channel stems of every
+// model in the zoo): rows = output pixels (n,p,q), columns = (r,s,c) padded with zeros to Kpad (multiple of 8).
+// The result feeds mpb_tc_gemm for fprop (A operand, K-major) and wgrad (B operand, MN-major) -- the TMA im2col
+// mode needs 16-byte pixel rows, which a 3-channel NHWC tensor does not have.
+// ------------------------------------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) im2col_nhwc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out,
+                                                          int N, int H, int W, int C, int R, int S, int P, int Q,
+                                                          int stride, int pad_h, int pad_w, int Kpad) {
+  extern __shared__ int tab[];          // per column: r | s<<8 | c<<16, or -1 for padding columns
+  const int Kreal = R * S * C;
+  for (int j = threadIdx.x; j < Kpad; j += blockDim.x) {
+    if (j < Kreal) { const int c = j % C, t = j / C; tab[j] = (t / S) | ((t % S) << 8) | (c << 16); }
+    else tab[j] = -1;
+  }
+  __syncthreads();
+  const int chunks = Kpad / 8;
+  const long long total = (long long)N * P * Q * chunks;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int ch = (int)(i % chunks);
+    const long long m = i / chunks;
+    const int q = (int)(m % Q);
+    const int pp = (int)((m / Q) % P);
+    const int n = (int)(m / ((long long)Q * P));
+    const int h0 = pp * stride - pad_h, w0 = q * stride - pad_w;
+    uint4 u;
+    __nv_bfloat16* v = reinterpret_cast<__nv_bfloat16*>(&u);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int t = tab[ch * 8 + k];
+      __nv_bfloat16 val = __float2bfloat16_rn(0.f);
+      if (t >= 0) {
+        const int h = h0 + (t & 0xff), w = w0 + ((t >> 8) & 0xff);
+        if (h >= 0 && h < H && w >= 0 && w < W) val = x[(((long long)n * H + h) * W + w) * C + (t >> 16)];
+      }
+      v[k] = val;
+    }
+    *reinterpret_cast<uint4*>(out + m * Kpad + ch * 8) = u;
+  }
+}
+}  // namespace
+
+MPB_API int mpb_im2col_nhwc(const void* x, void* out, int N, int H, int W, int C, int R, int S, int P, int Q, int stride,
+                            int pad_h, int pad_w, int Kpad, void* stream) {
+  if (Kpad % 8 != 0 || Kpad < R * S * C || R > 255 || S > 255 || C > 32767) return -2;
+  const long long total = (long long)N * P * Q * (Kpad / 8);
+  if (total <= 0) return 0;
+  im2col_nhwc_kernel<<<grid_for(total, 256, 16), 256, Kpad * sizeof(int), (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)out, N, H, W, C, R, S, P, Q, stride, pad_h, pad_w, Kpad);
+  MPB_CHECK_LAUNCH();
+  return 0;
 }

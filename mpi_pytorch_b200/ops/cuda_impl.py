@@ -91,8 +91,12 @@ class _ConvFn(torch.autograd.Function):
         ctx.weight_param = weight if getattr(weight, "_mpb_grad_ready", None) is not None else None
         tc = _gemm()
         stats = None
+        ctx.xcol = None
         if tc.fprop_ok(x, w, stride, padding, dilation, groups):
             y, stats = tc.conv_fprop(x, w, None if bias is None else bias.detach(), stride, padding, want_stats)
+        elif tc.im2col_ok(x, w, stride, padding, dilation, groups):
+            y, stats, ctx.xcol = tc.conv_fprop_im2col(x, w, None if bias is None else bias.detach(), stride, padding,
+                                                      want_stats)
         else:
             _note_fallback("conv_fprop")
             b = None if bias is None else bias.detach().to(x.dtype)
@@ -116,6 +120,9 @@ class _ConvFn(torch.autograd.Function):
         if need_x and tc.dgrad_ok(*args):
             gx = tc.conv_dgrad(gy, w, x.shape, stride, padding)
             need_x = False
+        if need_w and ctx.xcol is not None:
+            gw = tc.conv_wgrad_im2col(gy, ctx.xcol, w.shape).to(wdtype)
+            need_w = False
         if need_w and tc.wgrad_ok(*args):
             wp = ctx.weight_param
             if wp is not None and wp.grad is not None and wp.grad.dtype == torch.float32 \

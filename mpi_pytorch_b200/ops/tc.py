@@ -37,7 +37,8 @@ def _check(rc: int, what: str) -> None:
 
 # ----------------------------------------------------------------------------------------------- GEMM
 def gemm(a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int, a_mn: bool, b_mn: bool,
-         bias: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16, splitk: int = 1) -> torch.Tensor:
+         bias: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16, splitk: int = 1,
+         stats: Optional[torch.Tensor] = None) -> torch.Tensor:
     """D[m,n] = A[m,k] @ B[n,k]^T.  ``a`` is stored [m][k] (a_mn False) or [k][m] (True); same for ``b``."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_contiguous() and b.is_contiguous()
     if splitk > 1:
@@ -46,7 +47,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int, a_mn: bool, b
     else:
         d = torch.empty((m, n), dtype=out_dtype, device=a.device)
         mode = 0 if out_dtype == torch.bfloat16 else 1
-    rc = _LIB.mpb_tc_gemm(_p(a), _p(b), _p(d), _p(bias), c_int(m), c_int(n), c_int(k), c_ll(a.stride(0)),
+    rc = _LIB.mpb_tc_gemm(_p(a), _p(b), _p(d), _p(bias), _p(stats), c_int(m), c_int(n), c_int(k), c_ll(a.stride(0)),
                           c_ll(b.stride(0)), c_ll(n), c_int(int(a_mn)), c_int(int(b_mn)), c_int(mode), c_int(splitk),
                           c_void_p(_stream()))
     LAUNCHES["n"] += 1
@@ -156,3 +157,51 @@ def conv_wgrad(gy, x, w_shape, stride, padding, out: Optional[torch.Tensor] = No
     if out is not None:
         return out
     return dw.permute(0, 3, 1, 2)          # logical (K,C,R,S), physical KRSC
+
+
+# ------------------------------------------------------------------------ explicit-im2col path (C % 8 != 0)
+def _kpad(c: int, r: int, s: int) -> int:
+    return (c * r * s + 7) // 8 * 8
+
+
+def im2col_ok(x, w, stride, padding, dilation, groups) -> bool:
+    """3-channel stems and other inputs the TMA im2col mode cannot address (pixel rows < 16 bytes)."""
+    if not ENABLED or groups != 1 or tuple(dilation) != (1, 1) or stride[0] != stride[1]:
+        return False
+    if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or x.dim() != 4 or w.shape[0] % 8 != 0:
+        return False
+    return x.is_contiguous(memory_format=torch.channels_last) and w.shape[2] < 256 and w.shape[3] < 256
+
+
+def im2col(x, w_shape, stride, padding) -> torch.Tensor:
+    n, c, h, wd, k, r, s, p, q = _geom(x.shape, w_shape, stride, padding)
+    kp = _kpad(c, r, s)
+    out = torch.empty((n * p * q, kp), dtype=torch.bfloat16, device=x.device)
+    rc = _LIB.mpb_im2col_nhwc(_p(x), _p(out), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(r), c_int(s), c_int(p),
+                              c_int(q), c_int(stride[0]), c_int(padding[0]), c_int(padding[1]), c_int(kp),
+                              c_void_p(_stream()))
+    LAUNCHES["n"] += 1
+    _check(rc, "mpb_im2col_nhwc")
+    return out
+
+
+def conv_fprop_im2col(x, w, bias, stride, padding, want_stats=False):
+    """fprop as im2col + tensor-core GEMM.  Returns (y NHWC, stats, xcol) -- xcol is kept for the wgrad GEMM."""
+    n, c, h, wd, k, r, s, p, q = _geom(x.shape, w.shape, stride, padding)
+    kp = _kpad(c, r, s)
+    xcol = im2col(x, w.shape, stride, padding)
+    wmat = torch.zeros((k, kp), dtype=torch.bfloat16, device=x.device)
+    wmat[:, : c * r * s] = w.permute(0, 2, 3, 1).reshape(k, c * r * s)          # KRSC flattened
+    stats = torch.zeros(2 * k, dtype=torch.float32, device=x.device) if want_stats else None
+    y2d = gemm(xcol, wmat, n * p * q, k, kp, False, False, None if bias is None else bias.float(), stats=stats)
+    y = y2d.view(n, p, q, k).permute(0, 3, 1, 2)                                  # logical NCHW, physical NHWC
+    return y, stats, xcol
+
+
+def conv_wgrad_im2col(gy, xcol, w_shape) -> torch.Tensor:
+    k, c, r, s = w_shape
+    m, kp = xcol.shape
+    gy2d = gy.permute(0, 2, 3, 1).reshape(m, k)
+    splitk = max(1, min(8 * SMS // max(1, (kp + 127) // 128), (m + 63) // 64 // 96))
+    dw = gemm(gy2d, xcol, k, kp, m, True, True, out_dtype=torch.float32, splitk=max(2, splitk))
+    return dw[:, : c * r * s].reshape(k, r, s, c).permute(0, 3, 1, 2)            # logical (K,C,R,S)

@@ -135,3 +135,24 @@ def test_every_zoo_member_trains_on_the_native_path(name, hw):
              if torch.equal(before[n], p.detach()) and float(tr.engine.layout.view(tr.engine.grad_arena, p).abs().max()) > 0]
     assert not stale, stale
     tr.close()
+
+
+@pytest.mark.parametrize("n,c,h,w,k,r,stride,pad", [(4, 3, 64, 64, 64, 7, 2, 3), (2, 3, 35, 35, 64, 11, 4, 2),
+                                                    (2, 3, 33, 33, 32, 3, 2, 0)])
+def test_stem_conv_via_im2col_gemm(n, c, h, w, k, r, stride, pad):
+    """3-channel stems: explicit im2col + tensor-core GEMM for fprop and wgrad."""
+    tc = _tc()
+    torch.manual_seed(2)
+    x = torch.randn(n, c, h, w, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, c, r, r, device="cuda") * 0.1).bfloat16().contiguous(memory_format=torch.channels_last)
+    xf, wf = x.float(), wt.float().requires_grad_(True)
+    yref = F.conv2d(xf, wf, None, stride, pad)
+    gy = torch.randn_like(yref).bfloat16().contiguous(memory_format=torch.channels_last)
+    yref.backward(gy.float())
+    st, pd = (stride, stride), (pad, pad)
+    assert tc.im2col_ok(x, wt, st, pd, (1, 1), 1) and not tc.fprop_ok(x, wt, st, pd, (1, 1), 1)
+    y, stats, xcol = tc.conv_fprop_im2col(x, wt, None, st, pd, True)
+    assert y.shape == yref.shape and _rel(y, yref) < 8e-3
+    assert _rel(stats[:k], yref.sum(dim=(0, 2, 3))) < 1e-4
+    dw = tc.conv_wgrad_im2col(gy, xcol, wt.shape)
+    assert dw.shape == wf.grad.shape and _rel(dw, wf.grad) < 2e-4
