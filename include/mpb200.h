@@ -88,6 +88,9 @@ int mpb_tc_conv_fprop(const void* x, const void* w, void* y, const float* bias, 
 /* dx for stride-1 convolutions; the filter is read in place as an MN-major operand (no transposed copy).      */
 int mpb_tc_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int K, int R, int S, int P,
                       int Q, int pad_h, int pad_w, void* stream);
+/* dx for stride >= 2: decomposed into stride^2 output-parity classes, each an implicit GEMM over the taps that reach it. */
+int mpb_tc_conv_dgrad_strided(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int K, int R, int S,
+                              int P, int Q, int stride, int pad_h, int pad_w, void* stream);
 /* dw[K,R,S,C] (fp32) += split-K partial sums; dw must hold zeros or a partial gradient to accumulate into.     */
 int mpb_tc_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R, int S,
                       int P, int Q, int stride, int pad_h, int pad_w, int dil, int splitk, void* stream);

@@ -126,7 +126,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_b
   return d;
 }
 
-enum Mode { MODE_GEMM = 0, MODE_FPROP = 1, MODE_DGRAD = 2, MODE_WGRAD = 3 };
+enum Mode { MODE_GEMM = 0, MODE_FPROP = 1, MODE_DGRAD = 2, MODE_WGRAD = 3, MODE_DGRAD_STRIDED = 4 };
 enum OutMode { OUT_BF16 = 0, OUT_F32 = 1, OUT_ATOMIC_F32 = 2 };
 
 struct TcParams {
@@ -148,6 +148,8 @@ struct TcParams {
   int tap_cols;             // wgrad: grid.y enumerates (tap, c-block); number of c-blocks per tap
   int Cin_total;            // wgrad: Cin (row stride pieces of dW)
   int stages;               // smem ring depth (fewer stages -> more co-resident CTAs per SM)
+  // strided dgrad, one launch per output parity class (ph, pw): valid filter taps r = r0 + st*i, s = s0 + st*j
+  int st, ph, pw, r0, s0, nr, ns, lower_h, lower_w, Hfull, Wfull;
 };
 
 __global__ void __launch_bounds__(kThreads, 4)
@@ -197,7 +199,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (elect_one()) {
         // pixel decomposition of the tile's first row (fprop / dgrad)
         int q0 = 0, p0 = 0, img0 = 0;
-        if (p.mode == MODE_FPROP || p.mode == MODE_DGRAD) {
+        if (p.mode == MODE_FPROP || p.mode == MODE_DGRAD || p.mode == MODE_DGRAD_STRIDED) {
           q0 = m0 % p.Wout;
           const int t = m0 / p.Wout;
           p0 = t % p.Hout;
@@ -229,6 +231,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int rr = tap / p.S, ss = tap % p.S;
             tma_load_im2col_4d(&tmA, &full_bar[st], sa, cb * BK, q0 - p.pad_w, p0 - p.pad_h, img0, (uint16_t)ss, (uint16_t)rr);
             const int r = p.R - 1 - rr, s = p.S - 1 - ss;
+            const int col = (r * p.S + s) * p.Cin_total + n0;
+            for (int j = 0; j < p.BN / 64; ++j) tma_load_2d(&tmB, &full_bar[st], sb + j * 8192, col + j * 64, cb * BK);
+          } else if (p.mode == MODE_DGRAD_STRIDED) {
+            // rows = (n, h', w') of one parity class; dy row = h' + lower_h + (nr-1-i) for filter row r = r0 + st*i
+            const int tap = kb / cblocks, cb = kb % cblocks;
+            const int ir = tap / p.ns, is = tap % p.ns;
+            tma_load_im2col_4d(&tmA, &full_bar[st], sa, cb * BK, q0 + p.lower_w, p0 + p.lower_h, img0,
+                               (uint16_t)(p.ns - 1 - is), (uint16_t)(p.nr - 1 - ir));
+            const int r = p.r0 + p.st * ir, s = p.s0 + p.st * is;
             const int col = (r * p.S + s) * p.Cin_total + n0;
             for (int j = 0; j < p.BN / 64; ++j) tma_load_2d(&tmB, &full_bar[st], sb + j * 8192, col + j * 64, cb * BK);
           } else {  // MODE_WGRAD: reduction over output pixels; kb = pixel chunk of 64
@@ -275,6 +286,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const bool row_ok = row < p.M;
       int col_base = n0;
       long long out_off = 0;
+      long long out_row = row;
+      if (p.mode == MODE_DGRAD_STRIDED && row_ok) {      // scatter to (n, st*h'+ph, st*w'+pw) of the full-resolution dx
+        const int wq = row % p.Wout, t = row / p.Wout;
+        const int hq = t % p.Hout, img = t / p.Hout;
+        out_row = ((long long)img * p.Hfull + (long long)p.st * hq + p.ph) * p.Wfull + (long long)p.st * wq + p.pw;
+      }
       if (p.mode == MODE_WGRAD) { col_base = cblk_fixed * p.BN; out_off = (long long)tap_fixed * p.Cin_total; }
       for (int c = 0; c < p.BN; c += 32) {
         uint32_t r[32];
@@ -311,7 +328,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const int ncols = min(32, p.N - (col_base + c));
           if (ncols > 0) {
             if (p.out_mode == OUT_BF16) {
-              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + (long long)row * p.ldd + out_off + col_base + c;
+              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + out_row * p.ldd + out_off + col_base + c;
               if (ncols == 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
 #pragma unroll
                 for (int j = 0; j < 32; j += 8) {
@@ -325,7 +342,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for (int j = 0; j < ncols; ++j) dst[j] = __float2bfloat16_rn(v[j]);
               }
             } else if (p.out_mode == OUT_F32) {
-              float* dst = reinterpret_cast<float*>(p.D) + (long long)row * p.ldd + out_off + col_base + c;
+              float* dst = reinterpret_cast<float*>(p.D) + out_row * p.ldd + out_off + col_base + c;
               if (ncols == 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
 #pragma unroll
                 for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
@@ -333,7 +350,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for (int j = 0; j < ncols; ++j) dst[j] = v[j];
               }
             } else {
-              float* dst = reinterpret_cast<float*>(p.D) + (long long)row * p.ldd + out_off + col_base + c;
+              float* dst = reinterpret_cast<float*>(p.D) + out_row * p.ldd + out_off + col_base + c;
               for (int j = 0; j < ncols; ++j) atomicAdd(dst + j, v[j]);
             }
           }
@@ -533,6 +550,44 @@ MPB_API int mpb_tc_conv_dgrad(const void* dy, const void* w, void* dx, int N, in
   if (rc) return rc - 1000;
   dim3 grid((p.M + BM - 1) / BM, (C + p.BN - 1) / p.BN, 1);
   return launch(ta, tb, p, grid, (cudaStream_t)stream);
+}
+
+// dx for strided convolutions (stride >= 2): one launch per output parity class; positions that no filter tap
+// reaches (e.g. 1x1 stride 2) stay zero (dx is cleared first).
+MPB_API int mpb_tc_conv_dgrad_strided(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int K, int R,
+                                      int S, int P, int Q, int stride, int pad_h, int pad_w, void* stream) {
+  int rc = load_driver_fns();
+  if (rc) return rc;
+  if (K % 8 != 0 || C % 8 != 0 || stride < 2) return -2;
+  cudaStream_t st = (cudaStream_t)stream;
+  MPB_CUDA(cudaMemsetAsync(dx, 0, (size_t)N * H * W * C * 2, st));
+  CUtensorMap tb;
+  rc = make_map_2d(&tb, w, K, (long long)R * S * C, (long long)R * S * C, 64, 64);
+  if (rc) return rc - 1000;
+  for (int ph = 0; ph < stride; ++ph)
+    for (int pw = 0; pw < stride; ++pw) {
+      const int Hp = (H - ph + stride - 1) / stride, Wp = (W - pw + stride - 1) / stride;
+      const int r0 = (ph + pad_h) % stride, s0 = (pw + pad_w) % stride;
+      const int nr = r0 < R ? (R - r0 + stride - 1) / stride : 0, ns = s0 < S ? (S - s0 + stride - 1) / stride : 0;
+      if (Hp <= 0 || Wp <= 0 || nr == 0 || ns == 0) continue;
+      TcParams p;
+      memset(&p, 0, sizeof(p));
+      p.mode = MODE_DGRAD_STRIDED; p.M = N * Hp * Wp; p.N = C; p.BN = (C > 64) ? 128 : 64; p.a_mn = 0; p.b_mn = 1;
+      p.num_kb = nr * ns * ((K + 63) / 64); p.kb_per_split = p.num_kb;
+      p.idesc = make_idesc(p.BN, 0, 1);
+      p.out_mode = OUT_BF16; p.D = dx; p.ldd = C;
+      p.C = K; p.R = R; p.S = S; p.Hout = Hp; p.Wout = Wp; p.Cin_total = C;
+      p.st = stride; p.ph = ph; p.pw = pw; p.r0 = r0; p.s0 = s0; p.nr = nr; p.ns = ns; p.Hfull = H; p.Wfull = W;
+      p.lower_h = (ph + pad_h - r0) / stride - (nr - 1);
+      p.lower_w = (pw + pad_w - s0) / stride - (ns - 1);
+      CUtensorMap ta;   // base pixel h' + lower_h for h' in [0, Hp): bounding box [lower, P + upper) with Hp positions
+      rc = make_map_im2col(&ta, dy, N, P, Q, K, p.lower_w, p.lower_h, Wp - Q + p.lower_w, Hp - P + p.lower_h, 1, BM);
+      if (rc) return rc;
+      dim3 grid((p.M + BM - 1) / BM, (C + p.BN - 1) / p.BN, 1);
+      rc = launch(ta, tb, p, grid, st);
+      if (rc) return rc;
+    }
+  return 0;
 }
 
 // dw[K,R,S,C] (fp32, pre-zeroed) += sum over pixels dy[n,p,q,k] * x[n, p*stride+r-pad, q*stride+s-pad, c]

@@ -99,7 +99,7 @@ def fprop_ok(x, w, stride, padding, dilation, groups) -> bool:
 
 
 def dgrad_ok(x, w, stride, padding, dilation, groups) -> bool:
-    return (_base_ok(x, w, stride, padding, dilation, groups) and stride[0] == 1 and x.shape[1] % 8 == 0
+    return (_base_ok(x, w, stride, padding, dilation, groups) and x.shape[1] % 8 == 0
             and w.shape[0] % 8 == 0 and padding[0] <= w.shape[2] - 1 and padding[1] <= w.shape[3] - 1)
 
 
@@ -126,6 +126,13 @@ def conv_fprop(x, w, bias, stride, padding, want_stats=False) -> Tuple[torch.Ten
 def conv_dgrad(gy, w, x_shape, stride, padding) -> torch.Tensor:
     n, c, h, wd, k, r, s, p, q = _geom(x_shape, w.shape, stride, padding)
     dx = torch.empty(tuple(x_shape), dtype=torch.bfloat16, device=gy.device, memory_format=torch.channels_last)
+    if stride[0] > 1:
+        rc = _LIB.mpb_tc_conv_dgrad_strided(_p(gy), _p(w), _p(dx), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k),
+                                            c_int(r), c_int(s), c_int(p), c_int(q), c_int(stride[0]), c_int(padding[0]),
+                                            c_int(padding[1]), c_void_p(_stream()))
+        LAUNCHES["n"] += 1 + stride[0] * stride[0]
+        _check(rc, "mpb_tc_conv_dgrad_strided")
+        return dx
     rc = _LIB.mpb_tc_conv_dgrad(_p(gy), _p(w), _p(dx), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r),
                                 c_int(s), c_int(p), c_int(q), c_int(padding[0]), c_int(padding[1]), c_void_p(_stream()))
     LAUNCHES["n"] += 1

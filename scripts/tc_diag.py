@@ -104,7 +104,7 @@ def run_case(name):
         ms = timed(lambda: tc.conv_fprop(x, wt, None, st, pd, False))
         out["fprop_ms"], out["fprop_tflops"] = ms, flops / ms / 1e9
         out["cudnn_fprop_ms"] = timed(lambda: F.conv2d(x, wt, None, stride, pad))
-        if tc.dgrad_ok(x, wt, st, pd, (1, 1), 1):
+        if tc.dgrad_ok(x, wt, st, pd, (1, 1), 1):  # includes strided
             dx = tc.conv_dgrad(gy, wt, x.shape, st, pd)
             torch.cuda.synchronize()
             out["dgrad"] = err(dx, xf.grad)

@@ -43,7 +43,9 @@ CONVS = [(2, 64, 8, 8, 64, 1, 1, 0), (2, 64, 8, 8, 64, 3, 1, 1), (8, 64, 56, 56,
          (16, 512, 7, 7, 512, 3, 1, 1), (4, 64, 17, 17, 128, 3, 1, 0), (3, 128, 9, 11, 192, 5, 1, 2),
          # channel counts that are not multiples of 64 (DenseNet / Inception / SqueezeNet): TMA zero-fills the tails
          (4, 96, 12, 12, 48, 3, 1, 1), (4, 16, 13, 13, 64, 1, 1, 0), (2, 160, 9, 9, 192, 3, 1, 1),
-         (2, 288, 17, 17, 384, 3, 2, 0), (2, 80, 10, 10, 192, 3, 1, 0)]
+         (2, 288, 17, 17, 384, 3, 2, 0), (2, 80, 10, 10, 192, 3, 1, 0),
+         # more strided shapes: odd sizes, 5x5 stride 2, stride 3, 1x1 stride 2 on odd maps
+         (2, 64, 15, 15, 64, 5, 2, 2), (2, 64, 20, 20, 64, 3, 3, 1), (2, 64, 9, 9, 128, 1, 2, 0), (2, 64, 14, 14, 64, 7, 2, 3)]
 
 
 def test_conv_rect_kernels_inception():
@@ -78,10 +80,8 @@ def test_conv_fprop_dgrad_wgrad(n, c, h, w, k, r, stride, pad):
     assert _rel(y, yref) < 8e-3                                 # bf16 output rounding
     assert _rel(stats[:k], yref.sum(dim=(0, 2, 3))) < 1e-4      # stats come from the fp32 accumulator
     assert _rel(stats[k:], (yref * yref).sum(dim=(0, 2, 3))) < 1e-4
-    if tc.dgrad_ok(x, wt, st, pd, (1, 1), 1):
-        assert _rel(tc.conv_dgrad(gy, wt, x.shape, st, pd), xf.grad) < 8e-3
-    else:
-        assert stride != 1
+    assert tc.dgrad_ok(x, wt, st, pd, (1, 1), 1)                # stride 1 and strided (parity-decomposed) dgrad
+    assert _rel(tc.conv_dgrad(gy, wt, x.shape, st, pd), xf.grad) < 8e-3
     dw = tc.conv_wgrad(gy, x, wt.shape, st, pd)
     assert dw.shape == wf.grad.shape and _rel(dw, wf.grad) < 2e-4
     acc = torch.ones(k, r, r, c, device="cuda")                 # accumulate-into-arena form
