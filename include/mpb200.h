@@ -108,13 +108,22 @@ int mpb_ipc_handle_bytes(void);
 int mpb_signal_pad_bytes(void);
 int mpb_epoch_bytes(void);
 long long mpb_oneshot_max_elems(int blocks);
-/* algo 0 one-shot, 1 two-shot.  opt_kind 0: grads averaged in place; 1 Adam / 2 SGD-momentum: fp32 params and
+/* algo 0 one-shot, 1 two-shot, 2 two-shot through NVLS multicast addresses (mc_* = multicast views of the ranges).  opt_kind 0: grads averaged in place; 1 Adam / 2 SGD-momentum: fp32 params and
  * optional bf16 shadows updated on every rank from the averaged gradient (two-shot: owner slice + all-gather).
  * step_dev: optional device int holding the optimizer step (used instead of `step` when non-null).            */
 int mpb_allreduce_fused(void* const* grads, void* const* params, void* const* shadows, void* const* pads,
                         void* epochs, float* m, float* v, long long n, int rank, int W, int algo, int blocks,
                         int opt_kind, int step, float lr, float b1, float b2, float eps, float wd, float momentum,
-                        const int* step_dev, void* stream);
+                        const int* step_dev, void* mc_grads, void* mc_params, void* mc_shadow, void* stream);
+/* VMM / NVLS multicast symmetric memory (file descriptors are exchanged by the caller, e.g. over SCM_RIGHTS). */
+int mpb_vmm_multicast_supported(void);
+long long mpb_vmm_round_size(long long bytes, int num_devices);
+int mpb_vmm_alloc(long long bytes, void** ptr, int* fd_out, unsigned long long* handle_out);
+int mpb_vmm_import(int fd, long long bytes, void** ptr);
+int mpb_mc_create(long long bytes, int num_devices, int* fd_out, unsigned long long* mc_out);
+int mpb_mc_import(int fd, unsigned long long* mc_out);
+int mpb_mc_add_device(unsigned long long mc);
+int mpb_mc_bind_map(unsigned long long mc, unsigned long long mem_handle, long long bytes, void** mc_ptr);
 int mpb_broadcast(void* const* bufs, void* const* pads, void* epochs, long long n_floats, int rank, int W, int root,
                   int blocks, void* stream);
 int mpb_allgather_slices(void* const* bufs, void* const* pads, void* epochs, long long n_floats, int rank, int W,

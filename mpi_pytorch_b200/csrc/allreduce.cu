@@ -58,6 +58,20 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
 __device__ __forceinline__ void st_peer_f4(float* p, const float4& v) {
   asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
+// NVLS: one load returns the sum over every GPU bound to the multicast object (reduced inside the NVSwitch), one
+// store is replicated to all of them.
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void multimem_st_bf16x4(void* mc, const uint2& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(mc), "r"(v.x), "r"(v.y) : "memory");
+}
 __device__ __forceinline__ void st_peer_u2(void* p, const uint2& v) {
   asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
 }
@@ -94,8 +108,9 @@ struct ArParams {
   uint32_t* epochs;   // local, [MPB_MAX_COMM_BLOCKS]
   float* m; float* v; // local optimizer state (bucket-offset)
   long long n;        // elements in the bucket (multiple of 4*W)
-  int rank, W, algo;  // algo 0 = one-shot, 1 = two-shot
+  int rank, W, algo;  // algo 0 = one-shot, 1 = two-shot, 2 = two-shot through NVLS multicast addresses
   float scale;        // 1/W
+  float* mc_grads; float* mc_params; __nv_bfloat16* mc_shadow;   // multicast views of the same ranges (algo 2)
   OptArgs opt;
 };
 
@@ -153,6 +168,48 @@ __global__ void __launch_bounds__(MPB_COMM_THREADS, 1) allreduce_kernel(ArParams
         }
       }
     }
+  } else if (P.algo == 2) {
+    // ---- NVLS two-shot: the switch does the reduce-scatter (ld_reduce) and the all-gather (multicast store);
+    // each GPU moves only 1/W of the bucket over its links in each direction.
+    constexpr int U = 8;
+    const long long slice4 = (P.n / W) >> 2;
+    const long long base4 = slice4 * P.rank;
+    for (long long j0 = 0; j0 < slice4; j0 += nthreads * U) {
+      float4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long j = j0 + (long long)u * nthreads + tid;
+        if (j < slice4) v[u] = multimem_ld_reduce_f4(P.mc_grads + (base4 + j) * 4);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long j = j0 + (long long)u * nthreads + tid;
+        if (j >= slice4) continue;
+        const long long i4 = base4 + j;
+        float4 s = v[u];
+        s.x *= P.scale; s.y *= P.scale; s.z *= P.scale; s.w *= P.scale;
+        if (P.opt.kind == 0) {
+          multimem_st_f4(P.mc_grads + i4 * 4, s);
+        } else {
+          float* pp = reinterpret_cast<float*>(P.params.p[P.rank]) + i4 * 4;
+          float4 p4 = *reinterpret_cast<float4*>(pp);
+          float4 m4 = *reinterpret_cast<float4*>(P.m + i4 * 4);
+          float4 v4 = P.opt.kind == 1 ? *reinterpret_cast<float4*>(P.v + i4 * 4) : make_float4(0, 0, 0, 0);
+          p4.x = opt_one(p4.x, s.x, m4.x, v4.x, P.opt); p4.y = opt_one(p4.y, s.y, m4.y, v4.y, P.opt);
+          p4.z = opt_one(p4.z, s.z, m4.z, v4.z, P.opt); p4.w = opt_one(p4.w, s.w, m4.w, v4.w, P.opt);
+          *reinterpret_cast<float4*>(P.m + i4 * 4) = m4;
+          if (P.opt.kind == 1) *reinterpret_cast<float4*>(P.v + i4 * 4) = v4;
+          multimem_st_f4(P.mc_params + i4 * 4, p4);
+          if (P.mc_shadow) {
+            uint2 uu;
+            *reinterpret_cast<__nv_bfloat162*>(&uu.x) = __floats2bfloat162_rn(p4.x, p4.y);
+            *reinterpret_cast<__nv_bfloat162*>(&uu.y) = __floats2bfloat162_rn(p4.z, p4.w);
+            multimem_st_bf16x4(P.mc_shadow + i4 * 4, uu);
+          }
+        }
+      }
+    }
+    rank_barrier(P.pads, P.rank, W, e0 + 2);
   } else {
     // ---- two-shot: my slice only; result pushed to every peer.  U vectors per thread per trip keep
     // 16 x 16 B peer loads in flight per thread (NVLink latency ~2-3 us needs ~2 MB in flight per GPU).
@@ -299,11 +356,13 @@ MPB_API long long mpb_oneshot_max_elems(int blocks) { return (long long)blocks *
 MPB_API int mpb_allreduce_fused(void* const* grads, void* const* params, void* const* shadows, void* const* pads,
                                 void* epochs, float* m, float* v, long long n, int rank, int W, int algo, int blocks,
                                 int opt_kind, int step, float lr, float b1, float b2, float eps, float wd,
-                                float momentum, const int* step_dev, void* stream) {
+                                float momentum, const int* step_dev, void* mc_grads, void* mc_params, void* mc_shadow,
+                                void* stream) {
   if (W < 1 || W > MPB_MAX_WORLD || n <= 0 || (n % (4 * W)) != 0) return -1;
   if (blocks < 1) blocks = 1;
   if (blocks > MPB_MAX_COMM_BLOCKS) blocks = MPB_MAX_COMM_BLOCKS;
   if (algo == 0 && n > mpb_oneshot_max_elems(blocks)) return -2;
+  if (algo == 2 && (mc_grads == nullptr || (opt_kind != 0 && mc_params == nullptr))) return -3;
   ArParams P;
   memset(&P, 0, sizeof(P));
   for (int i = 0; i < W; ++i) {
@@ -313,6 +372,7 @@ MPB_API int mpb_allreduce_fused(void* const* grads, void* const* params, void* c
     P.pads.p[i] = pads[i];
   }
   P.epochs = (uint32_t*)epochs; P.m = m; P.v = v; P.n = n; P.rank = rank; P.W = W; P.algo = algo;
+  P.mc_grads = (float*)mc_grads; P.mc_params = (float*)mc_params; P.mc_shadow = (__nv_bfloat16*)mc_shadow;
   P.scale = 1.f / (float)W;
   P.opt.kind = opt_kind; P.opt.lr = lr; P.opt.b1 = b1; P.opt.b2 = b2; P.opt.eps = eps; P.opt.wd = wd;
   P.opt.momentum = momentum; P.opt.first_step = (step == 1); P.opt.step_ptr = step_dev;

@@ -18,6 +18,8 @@ GPU numerics tests exercise.
 from __future__ import annotations
 
 import ctypes
+import os
+import socket
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -38,8 +40,59 @@ class _RawCuda:
 
 
 class _SymBuf:
-    def __init__(self, base: int, nbytes: int, peers: List[int], tensor: torch.Tensor):
-        self.base, self.nbytes, self.peers, self.tensor = base, nbytes, peers, tensor
+    def __init__(self, base: int, nbytes: int, peers: List[int], tensor: torch.Tensor, mc: int = 0):
+        self.base, self.nbytes, self.peers, self.tensor, self.mc = base, nbytes, peers, tensor, mc
+
+
+class _FdRelay:
+    """Passes POSIX file descriptors (VMM / multicast handles) between the per-GPU processes.
+
+    Rank 0 listens on an abstract AF_UNIX socket; every other rank keeps one connection to it.  An exchange
+    sends each rank's descriptor to rank 0 (SCM_RIGHTS), which then hands every rank the full list."""
+
+    def __init__(self, world):
+        self.rank, self.size = world.rank, world.size
+        name = [None]
+        if self.rank == 0:
+            name[0] = "\0mpb-fd-{}-{}".format(os.getpid(), os.environ.get("MASTER_PORT", "0"))
+            self.srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            self.srv.bind(name[0])
+            self.srv.listen(self.size)
+        dist.broadcast_object_list(name, src=0)
+        self.conns: Dict[int, socket.socket] = {}
+        if self.rank == 0:
+            for _ in range(self.size - 1):
+                c, _addr = self.srv.accept()
+                r = int.from_bytes(c.recv(4), "little")
+                self.conns[r] = c
+        else:
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect(name[0])
+            c.sendall(self.rank.to_bytes(4, "little"))
+            self.conns[0] = c
+
+    def all_gather_fd(self, fd: int) -> List[int]:
+        """Every rank contributes one fd; returns the W descriptors (valid in this process) indexed by rank."""
+        if self.rank == 0:
+            fds = [fd] + [-1] * (self.size - 1)
+            for r, c in self.conns.items():
+                _msg, got, _flags, _addr = socket.recv_fds(c, 16, 1)
+                fds[r] = got[0]
+            for r, c in self.conns.items():
+                socket.send_fds(c, [b"fds"], fds)
+            return fds
+        c = self.conns[0]
+        socket.send_fds(c, [b"fd"], [fd])
+        _msg, got, _flags, _addr = socket.recv_fds(c, 16, self.size)
+        return list(got)
+
+    def broadcast_fd(self, fd: int) -> int:
+        if self.rank == 0:
+            for c in self.conns.values():
+                socket.send_fds(c, [b"mc"], [fd])
+            return fd
+        _msg, got, _flags, _addr = socket.recv_fds(self.conns[0], 16, 1)
+        return got[0]
 
 
 class PeerCollectives:
@@ -56,6 +109,18 @@ class PeerCollectives:
         self.launches = 0
         self.step_dev: Optional[torch.Tensor] = None    # device-resident optimizer step (set by the DP engine)
         torch.cuda.set_device(self.device)
+        self.lib.mpb_vmm_round_size.restype = c_ll
+        self.nvls = False
+        self._relay: Optional[_FdRelay] = None
+        if self.size > 1 and os.environ.get("MPB_NVLS", "1") != "0":
+            ok = torch.tensor([int(self.lib.mpb_vmm_multicast_supported())], device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 1:
+                try:
+                    self._relay = _FdRelay(world)
+                    self.nvls = True
+                except OSError:
+                    self.nvls = False
         pad_bytes = self.lib.mpb_signal_pad_bytes()
         self.pad = self._sym_alloc(pad_bytes)
         self.epochs = torch.zeros(self.lib.mpb_epoch_bytes() // 4, dtype=torch.int32, device=self.device)
@@ -65,7 +130,62 @@ class PeerCollectives:
             dist.barrier()
 
     # ------------------------------------------------------------------ symmetric memory
+    def _sym_alloc_vmm(self, nbytes: int) -> _SymBuf:
+        """VMM allocation shared by fd + an NVLS multicast object bound over all ranks' copies."""
+        size = int(self.lib.mpb_vmm_round_size(c_ll(nbytes), c_int(self.size)))
+        ptr, fd, handle = c_void_p(), c_int(-1), ctypes.c_ulonglong(0)
+        rc = self.lib.mpb_vmm_alloc(c_ll(size), ctypes.byref(ptr), ctypes.byref(fd), ctypes.byref(handle))
+        if rc != 0:
+            raise RuntimeError("mpb_vmm_alloc({}) failed: {}".format(size, rc))
+        base = int(ptr.value)
+        fds = self._relay.all_gather_fd(fd.value)
+        peers = []
+        for r in range(self.size):
+            if r == self.rank:
+                peers.append(base)
+                continue
+            p = c_void_p()
+            rc = self.lib.mpb_vmm_import(c_int(fds[r]), c_ll(size), ctypes.byref(p))
+            if rc != 0:
+                raise RuntimeError("mpb_vmm_import(rank {}) failed: {}".format(r, rc))
+            peers.append(int(p.value))
+        for r, f in enumerate(fds):
+            if f >= 0 and (r != self.rank or True):
+                try:
+                    os.close(f)
+                except OSError:
+                    pass
+        mc = ctypes.c_ulonglong(0)
+        if self.rank == 0:
+            mfd = c_int(-1)
+            rc = self.lib.mpb_mc_create(c_ll(size), c_int(self.size), ctypes.byref(mfd), ctypes.byref(mc))
+            if rc != 0:
+                raise RuntimeError("cuMulticastCreate failed: {}".format(rc))
+            self._relay.broadcast_fd(mfd.value)
+            os.close(mfd.value)
+        else:
+            mfd = self._relay.broadcast_fd(-1)
+            rc = self.lib.mpb_mc_import(c_int(mfd), ctypes.byref(mc))
+            os.close(mfd)
+            if rc != 0:
+                raise RuntimeError("multicast import failed: {}".format(rc))
+        rc = self.lib.mpb_mc_add_device(mc)
+        if rc != 0:
+            raise RuntimeError("cuMulticastAddDevice failed: {}".format(rc))
+        dist.barrier()                                   # every device added before anyone binds
+        mc_ptr = c_void_p()
+        rc = self.lib.mpb_mc_bind_map(mc, handle, c_ll(size), ctypes.byref(mc_ptr))
+        if rc != 0:
+            raise RuntimeError("cuMulticastBindMem/map failed: {}".format(rc))
+        dist.barrier()
+        t = torch.as_tensor(_RawCuda(base, size), device=self.device)
+        buf = _SymBuf(base, size, peers, t, int(mc_ptr.value))
+        self.bufs.append(buf)
+        return buf
+
     def _sym_alloc(self, nbytes: int) -> _SymBuf:
+        if self.nvls:
+            return self._sym_alloc_vmm(nbytes)
         nbytes = (int(nbytes) + 255) // 256 * 256
         ptr = c_void_p()
         rc = self.lib.mpb_sym_alloc(ctypes.byref(ptr), c_ll(nbytes))
@@ -114,12 +234,25 @@ class PeerCollectives:
             return (c_void_p * 1)(p)
         raise ValueError("tensor is not inside a symmetric arena obtained from PeerCollectives.alloc")
 
+    def _mc_ptr(self, view: Optional[torch.Tensor]) -> int:
+        if view is None:
+            return 0
+        p = view.data_ptr()
+        for b in self.bufs:
+            if b.mc and b.base <= p < b.base + b.nbytes:
+                return b.mc + (p - b.base)
+        return 0
+
     # ------------------------------------------------------------------ collectives
     def _algo(self, algo: str, nbytes: int, numel: int) -> int:
         if algo == "oneshot":
             a = 0
-        elif algo in ("twoshot", "nvls"):
+        elif algo == "twoshot":
             a = 1
+        elif algo == "nvls":
+            a = 2 if self.nvls else 1
+        elif self.nvls and nbytes > ONESHOT_MAX_BYTES:
+            a = 2
         else:
             a = 0 if nbytes <= ONESHOT_MAX_BYTES else 1
         if a == 0 and numel > self.lib.mpb_oneshot_max_elems(c_int(self._blocks(numel, 0))):
@@ -146,12 +279,18 @@ class PeerCollectives:
         s = self._peer_ptrs(shadows)
         kind = 0 if hyper is None else (1 if hyper.kind == "adam" else 2)
         h = hyper or Hyper()
+        mc_g = mc_p = mc_s = 0
+        if a == 2:
+            mc_g, mc_p, mc_s = self._mc_ptr(grads), self._mc_ptr(params), self._mc_ptr(shadows)
+            if mc_g == 0 or (kind != 0 and mc_p == 0) or (shadows is not None and kind != 0 and mc_s == 0):
+                a = 1                                     # range not covered by a multicast mapping
         rc = self.lib.mpb_allreduce_fused(
             g, p, s, self._pads_arr, c_void_p(self.epochs.data_ptr()),
             c_void_p(0 if m is None else m.data_ptr()), c_void_p(0 if v is None else v.data_ptr()),
             c_ll(n), c_int(self.rank), c_int(self.size), c_int(a), c_int(blocks), c_int(kind), c_int(step),
             c_float(h.lr), c_float(h.beta1), c_float(h.beta2), c_float(h.eps), c_float(h.weight_decay),
             c_float(h.momentum), c_void_p(0 if self.step_dev is None else self.step_dev.data_ptr()),
+            c_void_p(mc_g), c_void_p(mc_p), c_void_p(mc_s),
             c_void_p(torch.cuda.current_stream().cuda_stream))
         self.launches += 1
         if rc != 0:

@@ -21,7 +21,9 @@ def main():
     W, r = w.size, w.rank
     ok = True
     results = {"world": W, "checks": [], "bandwidth": []}
-    for n, algo in ((1024, "oneshot"), (64 * 1024, "oneshot"), (1 << 20, "twoshot"), (8 << 20, "twoshot"), (1 << 16, "auto")):
+    results["nvls"] = bool(pc.nvls)
+    for n, algo in ((1024, "oneshot"), (64 * 1024, "oneshot"), (1 << 20, "twoshot"), (8 << 20, "twoshot"), (1 << 16, "auto"),
+                    (1 << 20, "nvls"), (8 << 20, "nvls")):
         n = n // (4 * W) * (4 * W)
         g = pc.alloc(n, torch.float32)
         torch.manual_seed(100 + r)
@@ -63,7 +65,9 @@ def main():
         n = int(mb * 2 ** 20 / 4) // (4 * W) * (4 * W)
         g = pc.alloc(n, torch.float32)
         t = torch.empty(n, device=w.device)
-        for name, fn in (("peer", lambda: pc.all_reduce_avg_(g, "auto")), ("nccl", lambda: dist.all_reduce(t))):
+        for name, fn in (("peer_twoshot", lambda: pc.all_reduce_avg_(g, "twoshot" if mb > 0.25 else "oneshot")),
+                         ("peer_auto(nvls)" if pc.nvls else "peer_auto", lambda: pc.all_reduce_avg_(g, "auto")),
+                         ("nccl", lambda: dist.all_reduce(t))):
             for _ in range(5):
                 fn()
             torch.cuda.synchronize(); dist.barrier()
