@@ -38,6 +38,11 @@ int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float* gamma,
                const float* save_invstd, float* dsum, void* dx, void* dres, float* dgamma, float* dbeta, long long M,
                int C, int relu, int dtype, void* stream);
 
+/* BN -> ReLU backward (no residual): the ReLU mask is recomputed from x, so the forward output is never read. */
+int mpb_bn_relu_bwd_recompute(const void* dz, const void* x, const float* gamma, const float* beta,
+                              const float* save_mean, const float* save_invstd, float* dsum, void* dx, float* dgamma,
+                              float* dbeta, long long M, int C, int dtype, void* stream);
+
 /* BatchNorm backward without caller scratch.  This entry point has no counterpart in the reference: it exists
  * for hosts that cannot allocate device memory themselves (all of the GPU already belongs to their own pool,
  * or the implicit synchronisation of cudaMalloc/cudaFree is not acceptable where they call us).  Same maths

@@ -248,6 +248,114 @@ MPB_API int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// BatchNorm+ReLU backward WITHOUT reading the forward output: for BN -> ReLU (no residual) the ReLU mask is
+// recomputed from x with the same fp32 expression the forward used (fmaf(x, gamma*invstd, beta - mean*gamma*invstd)
+// > 0), so each pass reads two tensors (dz, x) instead of three.  Two rows per thread per trip keep 4 independent
+// 16-byte loads in flight.
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+template <typename T>
+__global__ void __launch_bounds__(256) bn_bwd_reduce_rx_kernel(const T* __restrict__ dz, const T* __restrict__ x,
+                                                               const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                               const float* __restrict__ save_mean,
+                                                               const float* __restrict__ save_invstd, float* __restrict__ dsum,
+                                                               long long M, int C, int cvecs, int rows_per_block) {
+  extern __shared__ float smem[];
+  const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
+  float mean[8], istd[8], sc[8], sh[8], s0[8] = {0}, s1[8] = {0};
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cv * 8 + k;
+    mean[k] = save_mean[c]; istd[k] = save_invstd[c];
+    sc[k] = (gamma ? gamma[c] : 1.f) * istd[k];
+    sh[k] = (beta ? beta[c] : 0.f) - mean[k] * sc[k];
+  }
+  const long long stride = (long long)gridDim.x * rows_per_block;
+  for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += 2 * stride) {
+    float g[2][8], xv[2][8];
+    const bool two = m + stride < M;
+    load8(dz + m * C + cv * 8, g[0]);
+    load8(x + m * C + cv * 8, xv[0]);
+    if (two) { load8(dz + (m + stride) * C + cv * 8, g[1]); load8(x + (m + stride) * C + cv * 8, xv[1]); }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gg = fmaf(xv[u][k], sc[k], sh[k]) > 0.f ? g[u][k] : 0.f;
+        s0[k] += gg; s1[k] += gg * (xv[u][k] - mean[k]) * istd[k];
+      }
+    }
+  }
+  reduce_pair_to_global(s0, s1, dsum, dsum + C, cvecs, rows_per_block, smem);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bn_bwd_apply_rx_kernel(const T* __restrict__ dz, const T* __restrict__ x,
+                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                              const float* __restrict__ save_mean,
+                                                              const float* __restrict__ save_invstd,
+                                                              const float* __restrict__ dsum, T* __restrict__ dx,
+                                                              float* __restrict__ dgamma, float* __restrict__ dbeta, long long M,
+                                                              int C, int cvecs, int rows_per_block) {
+  const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
+  float mean[8], istd[8], sc[8], sh[8], b0[8], b1[8];
+  const float invM = 1.f / (float)M;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cv * 8 + k;
+    mean[k] = save_mean[c]; istd[k] = save_invstd[c];
+    sc[k] = (gamma ? gamma[c] : 1.f) * istd[k];
+    sh[k] = (beta ? beta[c] : 0.f) - mean[k] * sc[k];
+    b0[k] = dsum[c] * invM; b1[k] = dsum[C + c] * invM;
+    if (blockIdx.x == 0 && r == 0) {
+      if (dgamma) dgamma[c] = dsum[C + c];
+      if (dbeta) dbeta[c] = dsum[c];
+    }
+  }
+  const long long stride = (long long)gridDim.x * rows_per_block;
+  for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += 2 * stride) {
+    float g[2][8], xv[2][8];
+    const bool two = m + stride < M;
+    load8(dz + m * C + cv * 8, g[0]);
+    load8(x + m * C + cv * 8, xv[0]);
+    if (two) { load8(dz + (m + stride) * C + cv * 8, g[1]); load8(x + (m + stride) * C + cv * 8, xv[1]); }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (u == 1 && !two) break;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gg = fmaf(xv[u][k], sc[k], sh[k]) > 0.f ? g[u][k] : 0.f;
+        const float xhat = (xv[u][k] - mean[k]) * istd[k];
+        xv[u][k] = sc[k] * (gg - b0[k] - xhat * b1[k]);
+      }
+      store8(dx + (m + u * stride) * C + cv * 8, xv[u]);
+    }
+  }
+}
+}  // namespace
+
+// BN -> ReLU backward (no residual branch); the mask is recomputed from x, the forward output is not needed.
+MPB_API int mpb_bn_relu_bwd_recompute(const void* dz, const void* x, const float* gamma, const float* beta,
+                                      const float* save_mean, const float* save_invstd, float* dsum, void* dx,
+                                      float* dgamma, float* dbeta, long long M, int C, int dtype, void* stream) {
+  if (C % 8 != 0 || C > 2048) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));
+  const Map mp = make_map(C);
+  const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
+  const int g1 = rows_grid(M, mp.rows_per_block, 4), g2 = rows_grid(M, mp.rows_per_block, 8);
+  DISPATCH_T(dtype,
+             bn_bwd_reduce_rx_kernel<T><<<g1, mp.threads, smem, st>>>((const T*)dz, (const T*)x, gamma, beta, save_mean,
+                                                                      save_invstd, dsum, M, C, mp.cvecs, mp.rows_per_block);
+             bn_bwd_apply_rx_kernel<T><<<g2, mp.threads, 0, st>>>((const T*)dz, (const T*)x, gamma, beta, save_mean,
+                                                                  save_invstd, dsum, (T*)dx, dgamma, dbeta, M, C, mp.cvecs,
+                                                                  mp.rows_per_block);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // BatchNorm backward for callers that cannot allocate device memory.
 //
 // mpb_bn_bwd() needs 2*C floats of scratch (`dsum`) that the caller must allocate.  Some callers cannot do

@@ -80,6 +80,48 @@ __device__ __forceinline__ void tma_load_im2col_4d(const CUtensorMap* map, uint6
       "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
       ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h) : "memory");
 }
+// cta_group::2 variants: issued by either CTA of a pair, the bytes land in the issuing CTA's shared memory but
+// complete on the LEADER CTA's mbarrier (shared::cluster address with the peer bit cleared)
+__device__ __forceinline__ uint32_t leader_bar(uint64_t* bar) { return smem_u32(bar) & 0xFEFFFFFFu; }
+__device__ __forceinline__ void tma_load_2d_2sm(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(leader_bar(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col_4d_2sm(const CUtensorMap* map, uint64_t* bar, void* dst, int c, int w, int h,
+                                                       int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(leader_bar(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar, uint16_t mask) {   // arrives on `bar` in every CTA of mask
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
@@ -150,13 +192,17 @@ struct TcParams {
   int stages;               // smem ring depth (fewer stages -> more co-resident CTAs per SM)
   // strided dgrad, one launch per output parity class (ph, pw): valid filter taps r = r0 + st*i, s = s0 + st*j
   int st, ph, pw, r0, s0, nr, ns, lower_h, lower_w, Hfull, Wfull;
+  int cluster;              // 1, or 2: CTA pair (cta_group::2) computes a 256 x BN tile; each CTA stages its 128 A rows and HALF of B
 };
 
+// kTwo = CTA-pair (cta_group::2) build.  It is a separate instantiation because a kernel that contains
+// cta_group::2 instructions can only be launched with an even cluster size (plain launches fail with error 912).
+template <bool kTwo>
 __global__ void __launch_bounds__(kThreads, 4)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages][A 16KB][B BN*128B] | barriers
-  const int b_stage_bytes = p.BN * BK * 2;
+  const int b_stage_bytes = (p.BN / p.cluster) * BK * 2;   // a CTA pair splits the B tile between its two shared memories
   const int stage_bytes = A_STAGE_BYTES + b_stage_bytes;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   __shared__ uint64_t full_bar[8], empty_bar[8], tmem_full_bar;
@@ -187,10 +233,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     fence_barrier_init();
   }
   if (p.stats) for (int j = threadIdx.x; j < 256; j += blockDim.x) { stat_smem[0][j] = 0.f; stat_smem[1][j] = 0.f; }
-  if (warp == 1) tmem_alloc(&tmem_base_smem, tmem_cols);
+  constexpr bool two = kTwo;
+  if (warp == 1) { if constexpr (two) tmem_alloc_2sm(&tmem_base_smem, tmem_cols); else tmem_alloc(&tmem_base_smem, tmem_cols); }
   tc_fence_before();
   __syncthreads();
+  if constexpr (two) cluster_sync_all();     // both CTAs' barriers and TMEM exist before the pair starts signalling
   tc_fence_after();
+  uint32_t crank = 0u;
+  if constexpr (two) crank = cluster_ctarank();
   const uint32_t tmem_base = tmem_base_smem;
 
   if (nkb > 0) {
@@ -213,46 +263,56 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           mbar_wait(&empty_bar[st], ph ^ 1);
           uint8_t* sa = smem + (size_t)st * stage_bytes;
           uint8_t* sb = sa + A_STAGE_BYTES;
-          mbar_expect_tx(&full_bar[st], (uint32_t)stage_bytes);
+          // pair mode: every byte of both CTAs completes on the leader's barrier, which the leader arms for both
+          if constexpr (!two) mbar_expect_tx(&full_bar[st], (uint32_t)stage_bytes);
+          else { if (crank == 0) mbar_expect_tx(&full_bar[st], (uint32_t)(2 * stage_bytes)); }
+          uint64_t* fb = &full_bar[st];
+          auto LD2 = [&](const CUtensorMap* m, void* dst, int c0, int c1) {
+            if constexpr (two) tma_load_2d_2sm(m, fb, dst, c0, c1); else tma_load_2d(m, fb, dst, c0, c1);
+          };
+          auto LDI = [&](const CUtensorMap* m, void* dst, int c, int w, int h, int n, int ow, int oh) {
+            if constexpr (two) tma_load_im2col_4d_2sm(m, fb, dst, c, w, h, n, (uint16_t)ow, (uint16_t)oh);
+            else tma_load_im2col_4d(m, fb, dst, c, w, h, n, (uint16_t)ow, (uint16_t)oh);
+          };
+          // this CTA's share of the B tile: all BN columns, or the crank-th half of them in pair mode
+          const int bn_cta = p.BN / p.cluster, n_off = (int)crank * bn_cta, regions = bn_cta / 64;
           if (p.mode == MODE_GEMM) {
-            if (!p.a_mn) tma_load_2d(&tmA, &full_bar[st], sa, kb * BK, m0);
-            else { tma_load_2d(&tmA, &full_bar[st], sa, m0, kb * BK); tma_load_2d(&tmA, &full_bar[st], sa + 8192, m0 + 64, kb * BK); }
-            if (!p.b_mn) tma_load_2d(&tmB, &full_bar[st], sb, kb * BK, n0);
-            else for (int j = 0; j < p.BN / 64; ++j) tma_load_2d(&tmB, &full_bar[st], sb + j * 8192, n0 + j * 64, kb * BK);
+            if (!p.a_mn) LD2(&tmA, sa, kb * BK, m0);
+            else { LD2(&tmA, sa, m0, kb * BK); LD2(&tmA, sa + 8192, m0 + 64, kb * BK); }
+            if (!p.b_mn) LD2(&tmB, sb, kb * BK, n0 + n_off);
+            else for (int j = 0; j < regions; ++j) LD2(&tmB, sb + j * 8192, n0 + n_off + j * 64, kb * BK);
           } else if (p.mode == MODE_FPROP) {
             const int tap = kb / cblocks, cb = kb % cblocks;
             const int r = tap / p.S, s = tap % p.S;
-            tma_load_im2col_4d(&tmA, &full_bar[st], sa, cb * BK, q0 * p.stride - p.pad_w, p0 * p.stride - p.pad_h, img0,
-                               (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
-            tma_load_2d(&tmB, &full_bar[st], sb, tap * p.C + cb * BK, n0);
+            LDI(&tmA, sa, cb * BK, q0 * p.stride - p.pad_w, p0 * p.stride - p.pad_h, img0, s * p.dil, r * p.dil);
+            LD2(&tmB, sb, tap * p.C + cb * BK, n0 + n_off);
           } else if (p.mode == MODE_DGRAD) {
             // A = im2col(dy) with pad' = (R-1) - pad, taps (r'', s''); B = W[k][r][s][c] with r = R-1-r'', MN-major
-            const int tap = kb / cblocks, cb = kb % cblocks;       // cblocks = Cout/64 here
+            const int tap = kb / cblocks, cb = kb % cblocks;       // cblocks = ceil(Cout/64) here
             const int rr = tap / p.S, ss = tap % p.S;
-            tma_load_im2col_4d(&tmA, &full_bar[st], sa, cb * BK, q0 - p.pad_w, p0 - p.pad_h, img0, (uint16_t)ss, (uint16_t)rr);
+            LDI(&tmA, sa, cb * BK, q0 - p.pad_w, p0 - p.pad_h, img0, ss, rr);
             const int r = p.R - 1 - rr, s = p.S - 1 - ss;
-            const int col = (r * p.S + s) * p.Cin_total + n0;
-            for (int j = 0; j < p.BN / 64; ++j) tma_load_2d(&tmB, &full_bar[st], sb + j * 8192, col + j * 64, cb * BK);
+            const int col = (r * p.S + s) * p.Cin_total + n0 + n_off;
+            for (int j = 0; j < regions; ++j) LD2(&tmB, sb + j * 8192, col + j * 64, cb * BK);
           } else if (p.mode == MODE_DGRAD_STRIDED) {
             // rows = (n, h', w') of one parity class; dy row = h' + lower_h + (nr-1-i) for filter row r = r0 + st*i
             const int tap = kb / cblocks, cb = kb % cblocks;
             const int ir = tap / p.ns, is = tap % p.ns;
-            tma_load_im2col_4d(&tmA, &full_bar[st], sa, cb * BK, q0 + p.lower_w, p0 + p.lower_h, img0,
-                               (uint16_t)(p.ns - 1 - is), (uint16_t)(p.nr - 1 - ir));
+            LDI(&tmA, sa, cb * BK, q0 + p.lower_w, p0 + p.lower_h, img0, p.ns - 1 - is, p.nr - 1 - ir);
             const int r = p.r0 + p.st * ir, s = p.s0 + p.st * is;
-            const int col = (r * p.S + s) * p.Cin_total + n0;
-            for (int j = 0; j < p.BN / 64; ++j) tma_load_2d(&tmB, &full_bar[st], sb + j * 8192, col + j * 64, cb * BK);
+            const int col = (r * p.S + s) * p.Cin_total + n0 + n_off;
+            for (int j = 0; j < regions; ++j) LD2(&tmB, sb + j * 8192, col + j * 64, cb * BK);
           } else {  // MODE_WGRAD: reduction over output pixels; kb = pixel chunk of 64
             const int pix = kb * BK;
             const int q = pix % p.Wout;
             const int t = pix / p.Wout;
             const int pp = t % p.Hout, img = t / p.Hout;
-            tma_load_2d(&tmA, &full_bar[st], sa, m0, pix);
-            tma_load_2d(&tmA, &full_bar[st], sa + 8192, m0 + 64, pix);
+            LD2(&tmA, sa, m0, pix);
+            LD2(&tmA, sa + 8192, m0 + 64, pix);
             const int r = tap_fixed / p.S, s = tap_fixed % p.S;
-            for (int j = 0; j < p.BN / 64; ++j)
-              tma_load_im2col_4d(&tmB, &full_bar[st], sb + j * 8192, (cblk_fixed * (p.BN / 64) + j) * 64,
-                                 q * p.stride - p.pad_w, pp * p.stride - p.pad_h, img, (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+            for (int j = 0; j < regions; ++j)
+              LDI(&tmB, sb + j * 8192, cblk_fixed * p.BN + n_off + j * 64, q * p.stride - p.pad_w, pp * p.stride - p.pad_h,
+                  img, s * p.dil, r * p.dil);
           }
         }
       }
@@ -260,7 +320,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // ================================ MMA issuer ================================
       const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
       const uint32_t a_step = p.a_mn ? 128u : 2u, b_step = p.b_mn ? 128u : 2u;   // descriptor advance per K=16 (16 B units)
-      for (int i = 0; i < nkb; ++i) {
+      for (int i = 0; i < nkb && crank == 0; ++i) {      // in pair mode only the leader CTA issues (for both)
         const int st = i % stages;
         const uint32_t ph = (i / stages) & 1;
         mbar_wait(&full_bar[st], ph);
@@ -270,10 +330,17 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t sb = sa + A_STAGE_BYTES;
           const uint64_t adesc = make_desc(sa, a_lbo, 1024), bdesc = make_desc(sb, b_lbo, 1024);
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            umma_bf16(tmem_base, adesc + (uint64_t)(a_step * k), bdesc + (uint64_t)(b_step * k), p.idesc, (i | k) != 0);
-          umma_commit(&empty_bar[st]);                 // frees the smem stage once these MMAs retire
-          if (i == nkb - 1) umma_commit(&tmem_full_bar);
+          for (int k = 0; k < BK / 16; ++k) {
+            if constexpr (two) umma_bf16_2sm(tmem_base, adesc + (uint64_t)(a_step * k), bdesc + (uint64_t)(b_step * k), p.idesc, (i | k) != 0);
+            else umma_bf16(tmem_base, adesc + (uint64_t)(a_step * k), bdesc + (uint64_t)(b_step * k), p.idesc, (i | k) != 0);
+          }
+          if constexpr (!two) {
+            umma_commit(&empty_bar[st]);               // frees the smem stage once these MMAs retire
+            if (i == nkb - 1) umma_commit(&tmem_full_bar);
+          } else {                                     // ... in both CTAs of the pair
+            umma_commit_2sm(&empty_bar[st], 3);
+            if (i == nkb - 1) umma_commit_2sm(&tmem_full_bar, 3);
+          }
         }
         __syncwarp();
       }
@@ -368,9 +435,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   }
+  if constexpr (two) cluster_sync_all();     // the leader may still read this CTA's smem / signal its barriers until it is done
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, tmem_cols);
+    if constexpr (two) tmem_dealloc_2sm(tmem_base, tmem_cols); else tmem_dealloc(tmem_base, tmem_cols);
   }
 }
 
@@ -422,7 +490,7 @@ int make_map_im2col(CUtensorMap* m, const void* ptr, int N, int H, int W, int C,
   return r == CUDA_SUCCESS ? 0 : -(200 + (int)r);
 }
 
-uint32_t make_idesc(int BN, int a_mn, int b_mn) {
+uint32_t make_idesc(int BN, int a_mn, int b_mn, int m = BM) {
   uint32_t d = 0;
   d |= 1u << 4;                    // D format F32
   d |= 1u << 7;                    // A format BF16
@@ -430,7 +498,7 @@ uint32_t make_idesc(int BN, int a_mn, int b_mn) {
   d |= (uint32_t)(a_mn ? 1 : 0) << 15;
   d |= (uint32_t)(b_mn ? 1 : 0) << 16;
   d |= (uint32_t)(BN >> 3) << 17;
-  d |= (uint32_t)(BM >> 4) << 24;
+  d |= (uint32_t)(m >> 4) << 24;
   return d;
 }
 
@@ -448,17 +516,39 @@ int default_stages(int BN, int num_kb) {
   return s;
 }
 
+// CTA pairs need >= 2 M tiles, and a B share per CTA that is a whole number of 64-wide regions when B is MN-major
+int want_cluster(int m_tiles, int BN, int b_mn) {
+  if (env_int("MPB_TC_CLUSTER", 1) == 0 || m_tiles < 2) return 1;
+  if (b_mn ? (BN % 128 != 0) : (BN % 16 != 0)) return 1;
+  return 2;
+}
+
 int launch(const CUtensorMap& a, const CUtensorMap& b, TcParams p, dim3 grid, cudaStream_t st) {
-  p.stages = default_stages(p.BN, p.kb_per_split);
-  const int smem = p.stages * (A_STAGE_BYTES + p.BN * BK * 2) + 1024;
+  if (p.cluster < 1) p.cluster = 1;
+  if (p.cluster == 2) p.idesc = (p.idesc & ~(0x1Fu << 24)) | ((uint32_t)(2 * BM >> 4) << 24);   // UMMA M = 256 across the pair
+  p.stages = default_stages(p.BN / p.cluster, p.kb_per_split);
+  const int smem = p.stages * (A_STAGE_BYTES + (p.BN / p.cluster) * BK * 2) + 1024;
   static int configured = 0;
   if (configured < smem) {
-    cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 1024);
+    cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 1024);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(tc_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 1024);
     if (e != cudaSuccess) return (int)e;
     configured = 200 * 1024 + 1024;
   }
-  tc_gemm_kernel<<<grid, kThreads, smem, st>>>(a, b, p);
-  return (int)cudaGetLastError();
+  if (p.cluster == 1) {
+    tc_gemm_kernel<false><<<grid, kThreads, smem, st>>>(a, b, p);
+    return (int)cudaGetLastError();
+  }
+  grid.x = (grid.x + 1) / 2 * 2;              // CTA pairs along M; a padding CTA only sees out-of-range rows
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid; cfg.blockDim = dim3(kThreads); cfg.dynamicSmemBytes = (size_t)smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return (int)cudaLaunchKernelEx(&cfg, tc_gemm_kernel<true>, a, b, p);
 }
 
 int pick_bn(int n) {
@@ -497,7 +587,8 @@ MPB_API int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias
   CUtensorMap ta, tb;
   rc = a_mn ? make_map_2d(&ta, A, K, M, lda, 64, 64) : make_map_2d(&ta, A, M, K, lda, 64, BM);
   if (rc) return rc;
-  rc = b_mn ? make_map_2d(&tb, B, K, N, ldb, 64, 64) : make_map_2d(&tb, B, N, K, ldb, 64, p.BN);
+  p.cluster = want_cluster((M + BM - 1) / BM, p.BN, b_mn);
+  rc = b_mn ? make_map_2d(&tb, B, K, N, ldb, 64, 64) : make_map_2d(&tb, B, N, K, ldb, 64, p.BN / p.cluster);
   if (rc) return rc - 1000;
   dim3 grid((M + BM - 1) / BM, (N + p.BN - 1) / p.BN, (p.num_kb + p.kb_per_split - 1) / p.kb_per_split);
   return launch(ta, tb, p, grid, (cudaStream_t)stream);
@@ -521,7 +612,8 @@ MPB_API int mpb_tc_conv_fprop(const void* x, const void* w, void* y, const float
   CUtensorMap ta, tb;
   rc = make_map_im2col(&ta, x, N, H, W, C, -pad_w, -pad_h, pad_w - (S - 1) * dil, pad_h - (R - 1) * dil, stride, BM);
   if (rc) return rc;
-  rc = make_map_2d(&tb, w, K, (long long)R * S * C, (long long)R * S * C, 64, p.BN);
+  p.cluster = want_cluster((p.M + BM - 1) / BM, p.BN, 0);
+  rc = make_map_2d(&tb, w, K, (long long)R * S * C, (long long)R * S * C, 64, p.BN / p.cluster);
   if (rc) return rc - 1000;
   dim3 grid((p.M + BM - 1) / BM, (K + p.BN - 1) / p.BN, 1);
   return launch(ta, tb, p, grid, (cudaStream_t)stream);
@@ -536,6 +628,7 @@ MPB_API int mpb_tc_conv_dgrad(const void* dy, const void* w, void* dx, int N, in
   TcParams p;
   memset(&p, 0, sizeof(p));
   p.mode = MODE_DGRAD; p.M = N * H * W; p.N = C; p.BN = (C > 64) ? 128 : 64; p.a_mn = 0; p.b_mn = 1;
+  if (env_int("MPB_TC_BN", 0) == 256 && C % 256 == 0) p.BN = 256;
   p.num_kb = R * S * ((K + 63) / 64); p.kb_per_split = p.num_kb;
   p.idesc = make_idesc(p.BN, 0, 1);
   p.out_mode = OUT_BF16; p.D = dx; p.ldd = C;
@@ -546,6 +639,7 @@ MPB_API int mpb_tc_conv_dgrad(const void* dy, const void* w, void* dx, int N, in
   // (so that Q + upper - lower == W base pixels per row), cf. the dgrad corner rules of TMA im2col.
   rc = make_map_im2col(&ta, dy, N, P, Q, K, -p.pad_w, -p.pad_h, pad_w - (S - 1) + (W - Q), pad_h - (R - 1) + (H - P), 1, BM);
   if (rc) return rc;
+  p.cluster = want_cluster((p.M + BM - 1) / BM, p.BN, 1);
   rc = make_map_2d(&tb, w, K, (long long)R * S * C, (long long)R * S * C, 64, 64);
   if (rc) return rc - 1000;
   dim3 grid((p.M + BM - 1) / BM, (C + p.BN - 1) / p.BN, 1);
@@ -610,6 +704,7 @@ MPB_API int mpb_tc_conv_wgrad(const void* dy, const void* x, float* dw, int N, i
   CUtensorMap ta, tb;
   rc = make_map_2d(&ta, dy, npq, K, K, 64, 64);
   if (rc) return rc;
+  p.cluster = want_cluster((K + BM - 1) / BM, p.BN, 1);
   rc = make_map_im2col(&tb, x, N, H, W, C, -pad_w, -pad_h, pad_w - (S - 1) * dil, pad_h - (R - 1) * dil, stride, BK);
   if (rc) return rc - 1000;
   dim3 grid((K + BM - 1) / BM, R * S * p.tap_cols, (p.num_kb + p.kb_per_split - 1) / p.kb_per_split);

@@ -215,13 +215,15 @@ class _BNActFn(torch.autograd.Function):
         _call("mpb_bn_fwd_apply", _p(x), _p(res), _p(out), _p(sums), _p(gamma), _p(beta), _p(run_mean), _p(run_var),
               _p(save_mean), _p(save_invstd), c_ll(m), c_int(c), c_float(eps), c_float(momentum), c_int(int(relu)),
               c_int(int(training)), c_int(_dt(x)), c_void_p(_stream()))
-        ctx.save_for_backward(x, out, gamma, save_mean, save_invstd)
+        # BN -> ReLU without a residual: backward recomputes the mask from x, so `out` need not be kept for it
+        recompute = bool(relu) and residual is None and training and beta is not None
+        ctx.save_for_backward(x, None if recompute else out, gamma, beta if recompute else None, save_mean, save_invstd)
         ctx.conf = (relu, residual is not None, training, c, m)
         return out
 
     @staticmethod
     def backward(ctx, gz):
-        x, out, gamma, save_mean, save_invstd = ctx.saved_tensors
+        x, out, gamma, beta, save_mean, save_invstd = ctx.saved_tensors
         relu, has_res, training, c, m = ctx.conf
         if not training:
             raise RuntimeError("backward through eval-mode BatchNorm is not supported on the native path")
@@ -229,6 +231,13 @@ class _BNActFn(torch.autograd.Function):
         if gz.dtype != x.dtype:
             gz = gz.to(x.dtype)
         dx = torch.empty_like(x)
+        if out is None:                                   # recompute-mask variant: reads dz and x only
+            dsum = torch.empty(2 * c, dtype=torch.float32, device=x.device)
+            dgamma = torch.empty(c, dtype=torch.float32, device=x.device)
+            dbeta = torch.empty(c, dtype=torch.float32, device=x.device)
+            _call("mpb_bn_relu_bwd_recompute", _p(gz), _p(x), _p(gamma), _p(beta), _p(save_mean), _p(save_invstd), _p(dsum),
+                  _p(dx), _p(dgamma), _p(dbeta), c_ll(m), c_int(c), c_int(_dt(x)), c_void_p(_stream()), launches=3)
+            return dx, dgamma, dbeta, None, None, None, None, None, None, None, None
         dres = torch.empty_like(x) if has_res else None
         dsum = torch.empty(2 * c, dtype=torch.float32, device=x.device)
         dgamma = torch.empty(c, dtype=torch.float32, device=x.device)

@@ -22,6 +22,11 @@ GEMM_CASES = {
     "gemm_bmn": (256, 512, 1000, 0, 1),        # linear dX shape
     "gemm_amn_bmn": (1000, 512, 256, 1, 1),    # linear dW shape
     "gemm_amn_bmn_small": (128, 64, 64, 1, 1),
+    # GEMM twins of the conv layers (same M, N, K, tiled TMA instead of im2col TMA)
+    "twin_l1": (802816, 64, 576, 0, 0),
+    "twin_l2": (200704, 128, 1152, 0, 0),
+    "twin_l3": (50176, 256, 2304, 0, 0),
+    "twin_l4": (12544, 512, 4608, 0, 0),
 }
 CONV_CASES = {
     # name: (N, C, H, W, K, R, stride, pad)
