@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(const T* __restrict__
       }
     }
   }
+  // one row per trip: these streaming kernels are occupancy-bound (a 2-row unroll measured slower on B200)
   for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += (long long)gridDim.x * rows_per_block) {
     float v[8];
     load8(x + m * C + cv * 8, v);
@@ -250,8 +251,7 @@ MPB_API int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float
 // ---------------------------------------------------------------------------------------------------------
 // BatchNorm+ReLU backward WITHOUT reading the forward output: for BN -> ReLU (no residual) the ReLU mask is
 // recomputed from x with the same fp32 expression the forward used (fmaf(x, gamma*invstd, beta - mean*gamma*invstd)
-// > 0), so each pass reads two tensors (dz, x) instead of three.  Two rows per thread per trip keep 4 independent
-// 16-byte loads in flight.
+// > 0), so each pass reads two tensors (dz, x) instead of three.
 // ---------------------------------------------------------------------------------------------------------
 namespace {
 template <typename T>
@@ -270,6 +270,8 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_rx_kernel(const T* __restri
     sc[k] = (gamma ? gamma[c] : 1.f) * istd[k];
     sh[k] = (beta ? beta[c] : 0.f) - mean[k] * sc[k];
   }
+  // reduction pass: few registers are live, so two rows per trip (4 independent 16 B loads) pay off here (measured),
+  // unlike in the apply passes
   const long long stride = (long long)gridDim.x * rows_per_block;
   for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += 2 * stride) {
     float g[2][8], xv[2][8];
@@ -313,24 +315,17 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_rx_kernel(const T* __restric
       if (dbeta) dbeta[c] = dsum[c];
     }
   }
-  const long long stride = (long long)gridDim.x * rows_per_block;
-  for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += 2 * stride) {
-    float g[2][8], xv[2][8];
-    const bool two = m + stride < M;
-    load8(dz + m * C + cv * 8, g[0]);
-    load8(x + m * C + cv * 8, xv[0]);
-    if (two) { load8(dz + (m + stride) * C + cv * 8, g[1]); load8(x + (m + stride) * C + cv * 8, xv[1]); }
+  for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += (long long)gridDim.x * rows_per_block) {
+    float g[8], xv[8];
+    load8(dz + m * C + cv * 8, g);
+    load8(x + m * C + cv * 8, xv);
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      if (u == 1 && !two) break;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float gg = fmaf(xv[u][k], sc[k], sh[k]) > 0.f ? g[u][k] : 0.f;
-        const float xhat = (xv[u][k] - mean[k]) * istd[k];
-        xv[u][k] = sc[k] * (gg - b0[k] - xhat * b1[k]);
-      }
-      store8(dx + (m + u * stride) * C + cv * 8, xv[u]);
+    for (int k = 0; k < 8; ++k) {
+      const float gg = fmaf(xv[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
+      const float xhat = (xv[k] - mean[k]) * istd[k];
+      xv[k] = sc[k] * (gg - b0[k] - xhat * b1[k]);
     }
+    store8(dx + m * C + cv * 8, xv);
   }
 }
 }  // namespace
@@ -344,7 +339,7 @@ MPB_API int mpb_bn_relu_bwd_recompute(const void* dz, const void* x, const float
   MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));
   const Map mp = make_map(C);
   const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
-  const int g1 = rows_grid(M, mp.rows_per_block, 4), g2 = rows_grid(M, mp.rows_per_block, 8);
+  const int g1 = rows_grid(M, mp.rows_per_block, 8), g2 = rows_grid(M, mp.rows_per_block, 8);
   DISPATCH_T(dtype,
              bn_bwd_reduce_rx_kernel<T><<<g1, mp.threads, smem, st>>>((const T*)dz, (const T*)x, gamma, beta, save_mean,
                                                                       save_invstd, dsum, M, C, mp.cvecs, mp.rows_per_block);

@@ -68,20 +68,49 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ 
     int ho_lo = (h + g.ph - g.kh + g.sh) / g.sh; if (h + g.ph - g.kh + 1 <= 0) ho_lo = 0;
     int wo_lo = (w + g.pw - g.kw + g.sw) / g.sw; if (w + g.pw - g.kw + 1 <= 0) wo_lo = 0;
     const int ho_hi = min((h + g.ph) / g.sh, g.Ho - 1), wo_hi = min((w + g.pw) / g.sw, g.Wo - 1);
-    for (int ho = ho_lo; ho <= ho_hi; ++ho) {
-      const int r = h - (ho * g.sh - g.ph);
-      if (r < 0 || r >= g.kh) continue;
-      for (int wo = wo_lo; wo <= wo_hi; ++wo) {
-        const int s = w - (wo * g.sw - g.pw);
-        if (s < 0 || s >= g.kw) continue;
-        const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
-        const uint2 packed = *reinterpret_cast<const uint2*>(idx + o);
-        const unsigned char* bi = reinterpret_cast<const unsigned char*>(&packed);
-        float gy[8];
-        load8(dy + o, gy);
-        const unsigned char pos = (unsigned char)(r * g.kw + s);
+    if (ho_hi - ho_lo < 2 && wo_hi - wo_lo < 2) {
+      // common case (kernel <= 2*stride): at most 2x2 windows cover a pixel -- issue all candidate loads first
+      uint2 pk[4];
+      float gv[4][8];
+      bool ok[4];
+      unsigned char pos[4];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] += (bi[k] == pos) ? gy[k] : 0.f;
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          const int ho = ho_lo + a, wo = wo_lo + b, c4 = a * 2 + b;
+          const int r = h - (ho * g.sh - g.ph), s = w - (wo * g.sw - g.pw);
+          ok[c4] = ho <= ho_hi && wo <= wo_hi && r >= 0 && r < g.kh && s >= 0 && s < g.kw;
+          pos[c4] = (unsigned char)(r * g.kw + s);
+          if (ok[c4]) {
+            const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
+            pk[c4] = *reinterpret_cast<const uint2*>(idx + o);
+            load8(dy + o, gv[c4]);
+          }
+        }
+#pragma unroll
+      for (int c4 = 0; c4 < 4; ++c4) {
+        if (!ok[c4]) continue;
+        const unsigned char* bi = reinterpret_cast<const unsigned char*>(&pk[c4]);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += (bi[k] == pos[c4]) ? gv[c4][k] : 0.f;
+      }
+    } else {
+    for (int ho = ho_lo; ho <= ho_hi; ++ho) {
+        const int r = h - (ho * g.sh - g.ph);
+        if (r < 0 || r >= g.kh) continue;
+        for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+          const int s = w - (wo * g.sw - g.pw);
+          if (s < 0 || s >= g.kw) continue;
+          const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
+          const uint2 packed = *reinterpret_cast<const uint2*>(idx + o);
+          const unsigned char* bi = reinterpret_cast<const unsigned char*>(&packed);
+          float gy[8];
+          load8(dy + o, gy);
+          const unsigned char pos = (unsigned char)(r * g.kw + s);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += (bi[k] == pos) ? gy[k] : 0.f;
+        }
       }
     }
     store8(dx + i * 8, acc);

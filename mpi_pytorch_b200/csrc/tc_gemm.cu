@@ -192,6 +192,7 @@ struct TcParams {
   int stages;               // smem ring depth (fewer stages -> more co-resident CTAs per SM)
   // strided dgrad, one launch per output parity class (ph, pw): valid filter taps r = r0 + st*i, s = s0 + st*j
   int st, ph, pw, r0, s0, nr, ns, lower_h, lower_w, Hfull, Wfull;
+  int a_shift;              // experiment: A stage holds rows [m0 - a_shift, ...); the UMMA descriptor starts a_shift rows in
   int cluster;              // 1, or 2: CTA pair (cta_group::2) computes a 256 x BN tile; each CTA stages its 128 A rows and HALF of B
 };
 
@@ -203,7 +204,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages][A 16KB][B BN*128B] | barriers
   const int b_stage_bytes = (p.BN / p.cluster) * BK * 2;   // a CTA pair splits the B tile between its two shared memories
-  const int stage_bytes = A_STAGE_BYTES + b_stage_bytes;
+  const int a_bytes = A_STAGE_BYTES + (p.a_shift ? 2048 : 0);   // shifted-view experiment: 16 extra rows
+  const int stage_bytes = a_bytes + b_stage_bytes;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   __shared__ uint64_t full_bar[8], empty_bar[8], tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
@@ -262,7 +264,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t ph = (i / stages) & 1;
           mbar_wait(&empty_bar[st], ph ^ 1);
           uint8_t* sa = smem + (size_t)st * stage_bytes;
-          uint8_t* sb = sa + A_STAGE_BYTES;
+          uint8_t* sb = sa + a_bytes;
           // pair mode: every byte of both CTAs completes on the leader's barrier, which the leader arms for both
           if constexpr (!two) mbar_expect_tx(&full_bar[st], (uint32_t)stage_bytes);
           else { if (crank == 0) mbar_expect_tx(&full_bar[st], (uint32_t)(2 * stage_bytes)); }
@@ -277,7 +279,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           // this CTA's share of the B tile: all BN columns, or the crank-th half of them in pair mode
           const int bn_cta = p.BN / p.cluster, n_off = (int)crank * bn_cta, regions = bn_cta / 64;
           if (p.mode == MODE_GEMM) {
-            if (!p.a_mn) LD2(&tmA, sa, kb * BK, m0);
+            if (!p.a_mn) LD2(&tmA, sa, kb * BK, m0 - p.a_shift);
             else { LD2(&tmA, sa, m0, kb * BK); LD2(&tmA, sa + 8192, m0 + 64, kb * BK); }
             if (!p.b_mn) LD2(&tmB, sb, kb * BK, n0 + n_off);
             else for (int j = 0; j < regions; ++j) LD2(&tmB, sb + j * 8192, n0 + n_off + j * 64, kb * BK);
@@ -327,8 +329,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tc_fence_after();
         if (elect_one()) {
           const uint32_t sa = smem_u32(smem + (size_t)st * stage_bytes);
-          const uint32_t sb = sa + A_STAGE_BYTES;
-          const uint64_t adesc = make_desc(sa, a_lbo, 1024), bdesc = make_desc(sb, b_lbo, 1024);
+          const uint32_t sb = sa + a_bytes;
+          // Row-shifted view of the A stage: the descriptor simply starts a_shift rows (128 B each) in, base_offset
+          // stays 0.  Measured on B200: the 128B swizzle is a function of the absolute shared-memory address, so a
+          // start that is not 1024 B aligned still de-swizzles what TMA wrote (setting base_offset = (addr>>7)&7
+          // gives wrong results).  This is what lets one halo tile serve all taps of a filter.
+          const uint64_t adesc = make_desc(sa + (uint32_t)p.a_shift * 128u, a_lbo, 1024);
+          const uint64_t bdesc = make_desc(sb, b_lbo, 1024);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             if constexpr (two) umma_bf16_2sm(tmem_base, adesc + (uint64_t)(a_step * k), bdesc + (uint64_t)(b_step * k), p.idesc, (i | k) != 0);
@@ -527,7 +534,7 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, TcParams p, dim3 grid, cu
   if (p.cluster < 1) p.cluster = 1;
   if (p.cluster == 2) p.idesc = (p.idesc & ~(0x1Fu << 24)) | ((uint32_t)(2 * BM >> 4) << 24);   // UMMA M = 256 across the pair
   p.stages = default_stages(p.BN / p.cluster, p.kb_per_split);
-  const int smem = p.stages * (A_STAGE_BYTES + (p.BN / p.cluster) * BK * 2) + 1024;
+  const int smem = p.stages * (A_STAGE_BYTES + (p.a_shift ? 2048 : 0) + (p.BN / p.cluster) * BK * 2) + 1024;
   static int configured = 0;
   if (configured < smem) {
     cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 1024);
@@ -585,9 +592,10 @@ MPB_API int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias
   p.idesc = make_idesc(p.BN, a_mn, b_mn);
   p.out_mode = out_mode; p.D = D; p.ldd = ldd; p.bias = bias; p.stats = (splitk == 1) ? stats : nullptr;
   CUtensorMap ta, tb;
-  rc = a_mn ? make_map_2d(&ta, A, K, M, lda, 64, 64) : make_map_2d(&ta, A, M, K, lda, 64, BM);
+  p.a_shift = a_mn ? 0 : env_int("MPB_TC_ASHIFT", 0);
+  rc = a_mn ? make_map_2d(&ta, A, K, M, lda, 64, 64) : make_map_2d(&ta, A, M, K, lda, 64, BM + (p.a_shift ? 16 : 0));
   if (rc) return rc;
-  p.cluster = want_cluster((M + BM - 1) / BM, p.BN, b_mn);
+  p.cluster = p.a_shift ? 1 : want_cluster((M + BM - 1) / BM, p.BN, b_mn);
   rc = b_mn ? make_map_2d(&tb, B, K, N, ldb, 64, 64) : make_map_2d(&tb, B, N, K, ldb, 64, p.BN / p.cluster);
   if (rc) return rc - 1000;
   dim3 grid((M + BM - 1) / BM, (N + p.BN - 1) / p.BN, (p.num_kb + p.kb_per_split - 1) / p.kb_per_split);
@@ -719,37 +727,55 @@ MPB_API int mpb_tc_conv_wgrad(const void* dy, const void* x, float* dw, int N, i
 // mode needs 16-byte pixel rows, which a 3-channel NHWC tensor does not have.
 // ------------------------------------------------------------------------------------------------------------
 namespace {
+constexpr int IM2COL_QT = 64;   // output pixels (consecutive q of one output row) per CTA
+
+// One CTA = IM2COL_QT consecutive output pixels of one (n, p) row.  The R input rows they touch are staged in
+// shared memory with coalesced loads (each is one contiguous span of ((QT-1)*stride + S) * C elements), then every
+// thread assembles 8-element (16 B) column chunks from shared memory and stores them coalesced.
 __global__ void __launch_bounds__(256) im2col_nhwc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out,
                                                           int N, int H, int W, int C, int R, int S, int P, int Q,
-                                                          int stride, int pad_h, int pad_w, int Kpad) {
-  extern __shared__ int tab[];          // per column: r | s<<8 | c<<16, or -1 for padding columns
+                                                          int stride, int pad_h, int pad_w, int Kpad, int qtiles) {
+  extern __shared__ __align__(16) unsigned char im2col_smem[];
+  const int span_px = (IM2COL_QT - 1) * stride + S;
+  const int span = span_px * C;                                   // elements per staged input row
+  __nv_bfloat16* rows = reinterpret_cast<__nv_bfloat16*>(im2col_smem);            // [R][span]
+  int* tab = reinterpret_cast<int*>(im2col_smem + (((size_t)R * span * 2 + 15) / 16) * 16);   // [Kpad]: r<<20 | (s*C+c)
   const int Kreal = R * S * C;
-  for (int j = threadIdx.x; j < Kpad; j += blockDim.x) {
-    if (j < Kreal) { const int c = j % C, t = j / C; tab[j] = (t / S) | ((t % S) << 8) | (c << 16); }
-    else tab[j] = -1;
+  for (int j = threadIdx.x; j < Kpad; j += blockDim.x) tab[j] = j < Kreal ? (((j / (S * C)) << 20) | (j % (S * C))) : -1;
+  const int qt = blockIdx.x % qtiles;
+  const int pp = (blockIdx.x / qtiles) % P;
+  const int n = blockIdx.x / (qtiles * P);
+  const int q0 = qt * IM2COL_QT;
+  const int h0 = pp * stride - pad_h, w0 = q0 * stride - pad_w;
+  const __nv_bfloat16 zero = __float2bfloat16_rn(0.f);
+  // staging: each input row contributes one contiguous span; bounds become a [e_lo, e_hi) range (no per-element division)
+  const int e_lo = w0 < 0 ? -w0 * C : 0;
+  const int e_hi = min(span, (W - w0) * C);
+  for (int r = 0; r < R; ++r) {
+    const int h = h0 + r;
+    const bool h_ok = h >= 0 && h < H;
+    const __nv_bfloat16* src = x + (((long long)n * H + (h_ok ? h : 0)) * W + w0) * C;
+    __nv_bfloat16* dst = rows + r * span;
+    for (int e = threadIdx.x; e < span; e += blockDim.x) dst[e] = (h_ok && e >= e_lo && e < e_hi) ? src[e] : zero;
   }
   __syncthreads();
   const int chunks = Kpad / 8;
-  const long long total = (long long)N * P * Q * chunks;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int ch = (int)(i % chunks);
-    const long long m = i / chunks;
-    const int q = (int)(m % Q);
-    const int pp = (int)((m / Q) % P);
-    const int n = (int)(m / ((long long)Q * P));
-    const int h0 = pp * stride - pad_h, w0 = q * stride - pad_w;
+  const int nq = min(IM2COL_QT, Q - q0);
+  // a warp handles 8 pixels x 4 chunks: table reads are broadcast / conflict-free, pixel-strided row reads hit
+  // distinct banks, and the warp's stores are 8 rows x 64 contiguous bytes
+  const int qgroups = (nq + 7) / 8, cgroups = (chunks + 3) / 4;
+  const int lane = threadIdx.x & 31;
+  for (int grp = threadIdx.x >> 5; grp < qgroups * cgroups; grp += blockDim.x >> 5) {
+    const int ql = (grp % qgroups) * 8 + (lane >> 2), ch = (grp / qgroups) * 4 + (lane & 3);
+    if (ql >= nq || ch >= chunks) continue;
     uint4 u;
     __nv_bfloat16* v = reinterpret_cast<__nv_bfloat16*>(&u);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int t = tab[ch * 8 + k];
-      __nv_bfloat16 val = __float2bfloat16_rn(0.f);
-      if (t >= 0) {
-        const int h = h0 + (t & 0xff), w = w0 + ((t >> 8) & 0xff);
-        if (h >= 0 && h < H && w >= 0 && w < W) val = x[(((long long)n * H + h) * W + w) * C + (t >> 16)];
-      }
-      v[k] = val;
+      v[k] = t >= 0 ? rows[(t >> 20) * span + ql * stride * C + (t & 0xFFFFF)] : zero;
     }
+    const long long m = ((long long)n * P + pp) * Q + q0 + ql;
     *reinterpret_cast<uint4*>(out + m * Kpad + ch * 8) = u;
   }
 }
@@ -758,10 +784,14 @@ __global__ void __launch_bounds__(256) im2col_nhwc_kernel(const __nv_bfloat16* _
 MPB_API int mpb_im2col_nhwc(const void* x, void* out, int N, int H, int W, int C, int R, int S, int P, int Q, int stride,
                             int pad_h, int pad_w, int Kpad, void* stream) {
   if (Kpad % 8 != 0 || Kpad < R * S * C || R > 255 || S > 255 || C > 32767) return -2;
-  const long long total = (long long)N * P * Q * (Kpad / 8);
-  if (total <= 0) return 0;
-  im2col_nhwc_kernel<<<grid_for(total, 256, 16), 256, Kpad * sizeof(int), (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x, (__nv_bfloat16*)out, N, H, W, C, R, S, P, Q, stride, pad_h, pad_w, Kpad);
+  if ((long long)N * P * Q <= 0) return 0;
+  const int qtiles = (Q + IM2COL_QT - 1) / IM2COL_QT;
+  const long long blocks = (long long)N * P * qtiles;
+  const size_t span = (size_t)((IM2COL_QT - 1) * stride + S) * C;
+  const size_t smem = (((size_t)R * span * 2 + 15) / 16) * 16 + (size_t)Kpad * sizeof(int);
+  if (blocks > 2147483647ll || smem > 48 * 1024) return -3;
+  im2col_nhwc_kernel<<<(unsigned)blocks, 256, smem, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)out, N, H, W, C, R, S, P, Q, stride, pad_h, pad_w, Kpad, qtiles);
   MPB_CHECK_LAUNCH();
   return 0;
 }
