@@ -111,10 +111,37 @@ def conv_supported(x, w, stride, padding, dilation, groups) -> bool:
     return fprop_ok(x, w, stride, padding, dilation, groups)
 
 
+_LIB.mpb_tc_halo_efficiency.restype = ctypes.c_float
+HALO = os.environ.get("MPB_TC_HALO", "1").lower() not in ("0", "false", "off")
+HALO_MIN_EFF = float(os.environ.get("MPB_TC_HALO_MIN_EFF", "0.6"))
+
+
+HALO_STREAMING = os.environ.get("MPB_TC_HALO_STREAMING", "0") == "1"   # also use the non-persistent halo kernel
+
+
+def halo_ok(out_h: int, out_w: int, r: int, s: int, stride, ci: int = 0, co: int = 0) -> bool:
+    """Stride-1 filters larger than 1x1 whose padded output rows tile the 128 GEMM rows well enough run on the
+    halo-tile kernel (activation tile fetched once per channel block instead of once per tap)."""
+    if not HALO or stride[0] != 1 or stride[1] != 1 or r * s == 1:
+        return False
+    if float(_LIB.mpb_tc_halo_efficiency(c_int(out_h), c_int(out_w), c_int(s))) < HALO_MIN_EFF:
+        return False
+    if HALO_STREAMING:
+        return True
+    return bool(_LIB.mpb_tc_halo_persistent_ok(c_int(ci), c_int(co), c_int(r), c_int(s), c_int(out_h), c_int(out_w)))
+
+
 def conv_fprop(x, w, bias, stride, padding, want_stats=False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     n, c, h, wd, k, r, s, p, q = _geom(x.shape, w.shape, stride, padding)
     y = torch.empty((n, k, p, q), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
     stats = torch.zeros(2 * k, dtype=torch.float32, device=x.device) if want_stats else None
+    if halo_ok(p, q, r, s, stride, c, k):
+        rc = _LIB.mpb_tc_conv_fprop_halo(_p(x), _p(w), _p(y), _p(None if bias is None else bias.float()), _p(stats),
+                                         c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r), c_int(s), c_int(p),
+                                         c_int(q), c_int(padding[0]), c_int(padding[1]), c_void_p(_stream()))
+        LAUNCHES["n"] += 1 + int(want_stats)
+        _check(rc, "mpb_tc_conv_fprop_halo")
+        return y, stats
     rc = _LIB.mpb_tc_conv_fprop(_p(x), _p(w), _p(y), _p(None if bias is None else bias.float()), _p(stats), c_int(n),
                                 c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r), c_int(s), c_int(p), c_int(q),
                                 c_int(stride[0]), c_int(padding[0]), c_int(padding[1]), c_int(1), c_void_p(_stream()))
@@ -132,6 +159,13 @@ def conv_dgrad(gy, w, x_shape, stride, padding) -> torch.Tensor:
                                             c_int(padding[1]), c_void_p(_stream()))
         LAUNCHES["n"] += 1 + stride[0] * stride[0]
         _check(rc, "mpb_tc_conv_dgrad_strided")
+        return dx
+    if halo_ok(h, wd, r, s, stride, k, c):
+        rc = _LIB.mpb_tc_conv_dgrad_halo(_p(gy), _p(w), _p(dx), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r),
+                                         c_int(s), c_int(p), c_int(q), c_int(padding[0]), c_int(padding[1]),
+                                         c_void_p(_stream()))
+        LAUNCHES["n"] += 1
+        _check(rc, "mpb_tc_conv_dgrad_halo")
         return dx
     rc = _LIB.mpb_tc_conv_dgrad(_p(gy), _p(w), _p(dx), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r),
                                 c_int(s), c_int(p), c_int(q), c_int(padding[0]), c_int(padding[1]), c_void_p(_stream()))
