@@ -43,6 +43,21 @@ int mpb_bn_relu_bwd_recompute(const void* dz, const void* x, const float* gamma,
                               const float* save_mean, const float* save_invstd, float* dsum, void* dx, float* dgamma,
                               float* dbeta, long long M, int C, int dtype, void* stream);
 
+/* Same kernels with the training-engine extras: `num_batches` (nullable) is the module's int64 step counter, bumped
+ * inside the forward kernel; `flags` bit 0 adds dgamma/dbeta to what the buffers hold (slots of the flat gradient
+ * arena) instead of overwriting them, bit 1 says `dsum` is already zero (skip the memset).                      */
+int mpb_bn_fwd_apply_ex(const void* x, const void* res, void* out, const float* sums, const float* gamma,
+                        const float* beta, float* run_mean, float* run_var, float* save_mean, float* save_invstd,
+                        long long* num_batches, long long M, int C, float eps, float momentum, int relu, int training,
+                        int dtype, void* stream);
+int mpb_bn_bwd_ex(const void* dz, const void* z, const void* x, const float* gamma, const float* save_mean,
+                  const float* save_invstd, float* dsum, void* dx, void* dres, float* dgamma, float* dbeta,
+                  long long M, int C, int relu, int flags, int dtype, void* stream);
+int mpb_bn_relu_bwd_recompute_ex(const void* dz, const void* x, const float* gamma, const float* beta,
+                                 const float* save_mean, const float* save_invstd, float* dsum, void* dx,
+                                 float* dgamma, float* dbeta, long long M, int C, int flags, int dtype,
+                                 void* stream);
+
 /* BatchNorm backward without caller scratch.  This entry point has no counterpart in the reference: it exists
  * for hosts that cannot allocate device memory themselves (all of the GPU already belongs to their own pool,
  * or the implicit synchronisation of cudaMalloc/cudaFree is not acceptable where they call us).  Same maths

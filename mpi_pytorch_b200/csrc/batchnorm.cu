@@ -72,8 +72,10 @@ __global__ void __launch_bounds__(256) bn_fwd_apply_kernel(const T* __restrict__
                                                            float* __restrict__ run_mean, float* __restrict__ run_var,
                                                            float* __restrict__ save_mean, float* __restrict__ save_invstd,
                                                            long long M, int C, int cvecs, int rows_per_block, float eps,
-                                                           float momentum, int relu, int training) {
+                                                           float momentum, int relu, int training,
+                                                           long long* __restrict__ num_batches) {
   const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
+  if (num_batches && training && blockIdx.x == 0 && threadIdx.x == 0) *num_batches += 1;
   float sc[8], sh[8];
   const float invM = 1.f / (float)M;
 #pragma unroll
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
                                                            const float* __restrict__ dsum, T* __restrict__ dx,
                                                            T* __restrict__ dres, float* __restrict__ dgamma,
                                                            float* __restrict__ dbeta, long long M, int C, int cvecs,
-                                                           int rows_per_block, int relu) {
+                                                           int rows_per_block, int relu, int accumulate) {
   const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
   float mean[8], istd[8], a[8], b0[8], b1[8];
   const float invM = 1.f / (float)M;
@@ -171,8 +173,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
     b0[k] = dsum[c] * invM;
     b1[k] = dsum[C + c] * invM;
     if (blockIdx.x == 0 && r == 0) {
-      if (dgamma) dgamma[c] = dsum[C + c];
-      if (dbeta) dbeta[c] = dsum[c];
+      if (dgamma) dgamma[c] = dsum[C + c] + (accumulate ? dgamma[c] : 0.f);
+      if (dbeta) dbeta[c] = dsum[c] + (accumulate ? dbeta[c] : 0.f);
     }
   }
   for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += (long long)gridDim.x * rows_per_block) {
@@ -214,27 +216,40 @@ MPB_API int mpb_bn_stats(const void* x, float* sums, long long M, int C, int dty
   return 0;
 }
 
-MPB_API int mpb_bn_fwd_apply(const void* x, const void* res, void* out, const float* sums, const float* gamma,
-                             const float* beta, float* run_mean, float* run_var, float* save_mean, float* save_invstd,
-                             long long M, int C, float eps, float momentum, int relu, int training, int dtype,
-                             void* stream) {
+// `num_batches` (may be null): the module's int64 num_batches_tracked counter, bumped by the kernel in training mode
+// so the step issues no separate elementwise launch for it.
+MPB_API int mpb_bn_fwd_apply_ex(const void* x, const void* res, void* out, const float* sums, const float* gamma,
+                                const float* beta, float* run_mean, float* run_var, float* save_mean,
+                                float* save_invstd, long long* num_batches, long long M, int C, float eps,
+                                float momentum, int relu, int training, int dtype, void* stream) {
   if (C % 8 != 0 || C > 2048) return -1;
   const Map mp = make_map(C);
   const int grid = rows_grid(M, mp.rows_per_block, 8);
   DISPATCH_T(dtype, bn_fwd_apply_kernel<T><<<grid, mp.threads, 0, (cudaStream_t)stream>>>(
                         (const T*)x, (const T*)res, (T*)out, sums, gamma, beta, run_mean, run_var, save_mean,
-                        save_invstd, M, C, mp.cvecs, mp.rows_per_block, eps, momentum, relu, training);)
+                        save_invstd, M, C, mp.cvecs, mp.rows_per_block, eps, momentum, relu, training, num_batches);)
   MPB_CHECK_LAUNCH();
   return 0;
 }
 
+MPB_API int mpb_bn_fwd_apply(const void* x, const void* res, void* out, const float* sums, const float* gamma,
+                             const float* beta, float* run_mean, float* run_var, float* save_mean, float* save_invstd,
+                             long long M, int C, float eps, float momentum, int relu, int training, int dtype,
+                             void* stream) {
+  return mpb_bn_fwd_apply_ex(x, res, out, sums, gamma, beta, run_mean, run_var, save_mean, save_invstd, nullptr, M, C,
+                             eps, momentum, relu, training, dtype, stream);
+}
+
 // dsum: 2*C floats scratch, zeroed here by the reduce call.
-MPB_API int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float* gamma, const float* save_mean,
-                       const float* save_invstd, float* dsum, void* dx, void* dres, float* dgamma, float* dbeta,
-                       long long M, int C, int relu, int dtype, void* stream) {
+// flags bit 0: dgamma/dbeta are added to what the buffers hold (they point into the gradient arena);
+// flags bit 1: `dsum` is already zero (a slice of the engine's per-step pre-zeroed pool) -- skip the memset.
+MPB_API int mpb_bn_bwd_ex(const void* dz, const void* z, const void* x, const float* gamma, const float* save_mean,
+                          const float* save_invstd, float* dsum, void* dx, void* dres, float* dgamma, float* dbeta,
+                          long long M, int C, int relu, int flags, int dtype, void* stream) {
   if (C % 8 != 0 || C > 2048) return -1;
   cudaStream_t st = (cudaStream_t)stream;
-  MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));
+  const int accumulate = flags & 1;
+  if (!(flags & 2)) MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));
   const Map mp = make_map(C);
   const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
   const int g1 = rows_grid(M, mp.rows_per_block, 4), g2 = rows_grid(M, mp.rows_per_block, 8);
@@ -243,9 +258,16 @@ MPB_API int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float
                                                                    save_invstd, dsum, M, C, mp.cvecs, mp.rows_per_block, relu);
              bn_bwd_apply_kernel<T><<<g2, mp.threads, 0, st>>>((const T*)dz, (const T*)z, (const T*)x, gamma, save_mean,
                                                                save_invstd, dsum, (T*)dx, (T*)dres, dgamma, dbeta, M, C,
-                                                               mp.cvecs, mp.rows_per_block, relu);)
+                                                               mp.cvecs, mp.rows_per_block, relu, accumulate);)
   MPB_CHECK_LAUNCH();
   return 0;
+}
+
+MPB_API int mpb_bn_bwd(const void* dz, const void* z, const void* x, const float* gamma, const float* save_mean,
+                       const float* save_invstd, float* dsum, void* dx, void* dres, float* dgamma, float* dbeta,
+                       long long M, int C, int relu, int dtype, void* stream) {
+  return mpb_bn_bwd_ex(dz, z, x, gamma, save_mean, save_invstd, dsum, dx, dres, dgamma, dbeta, M, C, relu, 0, dtype,
+                       stream);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -299,7 +321,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_rx_kernel(const T* __restric
                                                               const float* __restrict__ save_invstd,
                                                               const float* __restrict__ dsum, T* __restrict__ dx,
                                                               float* __restrict__ dgamma, float* __restrict__ dbeta, long long M,
-                                                              int C, int cvecs, int rows_per_block) {
+                                                              int C, int cvecs, int rows_per_block, int accumulate) {
   const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
   float mean[8], istd[8], sc[8], sh[8], b0[8], b1[8];
   const float invM = 1.f / (float)M;
@@ -311,8 +333,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_rx_kernel(const T* __restric
     sh[k] = (beta ? beta[c] : 0.f) - mean[k] * sc[k];
     b0[k] = dsum[c] * invM; b1[k] = dsum[C + c] * invM;
     if (blockIdx.x == 0 && r == 0) {
-      if (dgamma) dgamma[c] = dsum[C + c];
-      if (dbeta) dbeta[c] = dsum[c];
+      if (dgamma) dgamma[c] = dsum[C + c] + (accumulate ? dgamma[c] : 0.f);
+      if (dbeta) dbeta[c] = dsum[c] + (accumulate ? dbeta[c] : 0.f);
     }
   }
   for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += (long long)gridDim.x * rows_per_block) {
@@ -331,12 +353,14 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_rx_kernel(const T* __restric
 }  // namespace
 
 // BN -> ReLU backward (no residual branch); the mask is recomputed from x, the forward output is not needed.
-MPB_API int mpb_bn_relu_bwd_recompute(const void* dz, const void* x, const float* gamma, const float* beta,
-                                      const float* save_mean, const float* save_invstd, float* dsum, void* dx,
-                                      float* dgamma, float* dbeta, long long M, int C, int dtype, void* stream) {
+MPB_API int mpb_bn_relu_bwd_recompute_ex(const void* dz, const void* x, const float* gamma, const float* beta,
+                                         const float* save_mean, const float* save_invstd, float* dsum, void* dx,
+                                         float* dgamma, float* dbeta, long long M, int C, int flags, int dtype,
+                                         void* stream) {
   if (C % 8 != 0 || C > 2048) return -1;
   cudaStream_t st = (cudaStream_t)stream;
-  MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));
+  const int accumulate = flags & 1;
+  if (!(flags & 2)) MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));
   const Map mp = make_map(C);
   const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
   const int g1 = rows_grid(M, mp.rows_per_block, 8), g2 = rows_grid(M, mp.rows_per_block, 8);
@@ -345,9 +369,16 @@ MPB_API int mpb_bn_relu_bwd_recompute(const void* dz, const void* x, const float
                                                                       save_invstd, dsum, M, C, mp.cvecs, mp.rows_per_block);
              bn_bwd_apply_rx_kernel<T><<<g2, mp.threads, 0, st>>>((const T*)dz, (const T*)x, gamma, beta, save_mean,
                                                                   save_invstd, dsum, (T*)dx, dgamma, dbeta, M, C, mp.cvecs,
-                                                                  mp.rows_per_block);)
+                                                                  mp.rows_per_block, accumulate);)
   MPB_CHECK_LAUNCH();
   return 0;
+}
+
+MPB_API int mpb_bn_relu_bwd_recompute(const void* dz, const void* x, const float* gamma, const float* beta,
+                                      const float* save_mean, const float* save_invstd, float* dsum, void* dx,
+                                      float* dgamma, float* dbeta, long long M, int C, int dtype, void* stream) {
+  return mpb_bn_relu_bwd_recompute_ex(dz, x, gamma, beta, save_mean, save_invstd, dsum, dx, dgamma, dbeta, M, C, 0,
+                                      dtype, stream);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -404,7 +435,7 @@ MPB_API int mpb_bn_bwd_noalloc(const void* dz, const void* z, const void* x, con
                                                                    save_invstd, dsum, M, C, mp.cvecs, mp.rows_per_block, relu);
              bn_bwd_apply_kernel<T><<<g2, mp.threads, 0, st>>>((const T*)dz, (const T*)z, (const T*)x, gamma, save_mean,
                                                                save_invstd, dsum, (T*)dx, (T*)dres, dgamma, dbeta, M, C,
-                                                               mp.cvecs, mp.rows_per_block, relu);)
+                                                               mp.cvecs, mp.rows_per_block, relu, 0);)
   MPB_CHECK_LAUNCH();
   return 0;
 }

@@ -117,6 +117,137 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ 
   }
 }
 
+// 3x3 windows (every max pool in the zoo): the nine tap loads are issued before the first compare and stay packed
+// (16 bytes of registers per tap for bf16) until they are compared, so each thread keeps nine requests in flight at
+// <= 64 registers.
+template <typename T> struct Raw8;
+template <> struct Raw8<float> { float4 a, b; };
+template <> struct Raw8<__nv_bfloat16> { uint4 u; };
+__device__ __forceinline__ void load_raw(const float* p, Raw8<float>& r) {
+  r.a = *reinterpret_cast<const float4*>(p); r.b = *reinterpret_cast<const float4*>(p + 4);
+}
+__device__ __forceinline__ void load_raw(const __nv_bfloat16* p, Raw8<__nv_bfloat16>& r) {
+  r.u = *reinterpret_cast<const uint4*>(p);
+}
+__device__ __forceinline__ void unpack(const Raw8<float>& r, float (&v)[8]) {
+  v[0] = r.a.x; v[1] = r.a.y; v[2] = r.a.z; v[3] = r.a.w; v[4] = r.b.x; v[5] = r.b.y; v[6] = r.b.z; v[7] = r.b.w;
+}
+__device__ __forceinline__ void unpack(const Raw8<__nv_bfloat16>& r, float (&v)[8]) {
+  const unsigned w[4] = {r.u.x, r.u.y, r.u.z, r.u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256, sizeof(T) == 2 ? 4 : 2) maxpool3x3_fwd_kernel(const T* __restrict__ x,
+                                                                                     T* __restrict__ y,
+                                                                                     unsigned char* __restrict__ idx,
+                                                                                     PoolGeom g) {
+  const int cvecs = g.C / 8;
+  const long long total = (long long)g.N * g.Ho * g.Wo * cvecs;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const unsigned iu = (unsigned)i;
+    const int cv = (int)(iu % (unsigned)cvecs);
+    unsigned t = iu / (unsigned)cvecs;
+    const int wo = (int)(t % (unsigned)g.Wo); t /= (unsigned)g.Wo;
+    const int ho = (int)(t % (unsigned)g.Ho);
+    const int n = (int)(t / (unsigned)g.Ho);
+    const int h0 = ho * g.sh - g.ph, w0 = wo * g.sw - g.pw;
+    Raw8<T> raw[9];
+    unsigned okmask = 0;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int h = h0 + r, w = w0 + s;
+        if (h >= 0 && h < g.H && w >= 0 && w < g.W) {
+          okmask |= 1u << (r * 3 + s);
+          load_raw(x + (((long long)n * g.H + h) * g.W + w) * g.C + cv * 8, raw[r * 3 + s]);
+        }
+      }
+    float best[8];
+    unsigned bi_lo = 0, bi_hi = 0;                      // argmax bytes of channels 0..3 / 4..7
+#pragma unroll
+    for (int k = 0; k < 8; ++k) best[k] = -INFINITY;
+    bool first = true;
+#pragma unroll
+    for (int p = 0; p < 9; ++p) {
+      if (!((okmask >> p) & 1u)) continue;
+      float v[8];
+      unpack(raw[p], v);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (first || v[k] > best[k] || v[k] != v[k]) {   // torch: first max wins, NaN propagates
+          best[k] = v[k];
+          const int sft = 8 * (k & 3);
+          if (k < 4) bi_lo = (bi_lo & ~(0xFFu << sft)) | ((unsigned)p << sft);
+          else bi_hi = (bi_hi & ~(0xFFu << sft)) | ((unsigned)p << sft);
+        }
+      first = false;
+    }
+    const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
+    store8(y + o, best);
+    if (idx) *reinterpret_cast<uint2*>(idx + o) = make_uint2(bi_lo, bi_hi);
+  }
+}
+
+// 3x3 / stride 2 / pad 1 on even H, W (the ResNet / DenseNet stem pool): one thread owns a 2x2 quad of input pixels.
+// The quad (2a..2a+1, 2b..2b+1) is covered by exactly the four windows (a..a+1, b..b+1), so four (argmax, dy) loads
+// produce four outputs -- the per-pixel formulation needs nine loads for the same four pixels.
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool3x3s2_bwd_kernel(const T* __restrict__ dy,
+                                                               const unsigned char* __restrict__ idx,
+                                                               T* __restrict__ dx, PoolGeom g) {
+  const int cvecs = g.C / 8;
+  const long long total = (long long)g.N * g.Ho * g.Wo * cvecs;        // Ho = H/2, Wo = W/2 quads
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const unsigned iu = (unsigned)i;
+    const int cv = (int)(iu % (unsigned)cvecs);
+    unsigned t = iu / (unsigned)cvecs;
+    const int b = (int)(t % (unsigned)g.Wo); t /= (unsigned)g.Wo;
+    const int a = (int)(t % (unsigned)g.Ho);
+    const int n = (int)(t / (unsigned)g.Ho);
+    uint2 pk[4];
+    float gv[4][8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int ho = a + (q >> 1), wo = b + (q & 1);
+      if (ho < g.Ho && wo < g.Wo) {
+        const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
+        pk[q] = *reinterpret_cast<const uint2*>(idx + o);
+        load8(dy + o, gv[q]);
+      } else {
+        pk[q] = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);                   // position 255 never matches
+#pragma unroll
+        for (int k = 0; k < 8; ++k) gv[q][k] = 0.f;
+      }
+    }
+    float o00[8], o01[8], o10[8], o11[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int sft = 8 * (k & 3);
+      const unsigned p0 = ((k < 4 ? pk[0].x : pk[0].y) >> sft) & 0xFFu;
+      const unsigned p1 = ((k < 4 ? pk[1].x : pk[1].y) >> sft) & 0xFFu;
+      const unsigned p2 = ((k < 4 ? pk[2].x : pk[2].y) >> sft) & 0xFFu;
+      const unsigned p3 = ((k < 4 ? pk[3].x : pk[3].y) >> sft) & 0xFFu;
+      // window (a, b) sees the quad at taps (1..2, 1..2); (a, b+1) at (1..2, 0); (a+1, b) at (0, 1..2); (a+1, b+1) at (0, 0)
+      o00[k] = (p0 == 4 ? gv[0][k] : 0.f);
+      o01[k] = (p0 == 5 ? gv[0][k] : 0.f) + (p1 == 3 ? gv[1][k] : 0.f);
+      o10[k] = (p0 == 7 ? gv[0][k] : 0.f) + (p2 == 1 ? gv[2][k] : 0.f);
+      o11[k] = (p0 == 8 ? gv[0][k] : 0.f) + (p1 == 6 ? gv[1][k] : 0.f) + (p2 == 2 ? gv[2][k] : 0.f) +
+               (p3 == 0 ? gv[3][k] : 0.f);
+    }
+    const long long base = (((long long)n * g.H + 2 * a) * g.W + 2 * b) * g.C + cv * 8;
+    store8(dx + base, o00);
+    store8(dx + base + g.C, o01);
+    store8(dx + base + (long long)g.W * g.C, o10);
+    store8(dx + base + (long long)g.W * g.C + g.C, o11);
+  }
+}
+
 // avg pool; divisor semantics follow torch (count_include_pad with ceil_mode clipping).
 template <typename T, bool BWD>
 __global__ void __launch_bounds__(256) avgpool_kernel(const T* __restrict__ in, T* __restrict__ out, PoolGeom g,
@@ -292,7 +423,11 @@ MPB_API int mpb_maxpool_fwd(const void* x, void* y, unsigned char* idx, int N, i
   if ((long long)N * H * W * (C / 8) >= (1ll << 32)) return -3;
   const PoolGeom g = geom(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw);
   const long long total = (long long)N * Ho * Wo * (C / 8);
-  DISPATCH_T(dtype, maxpool_fwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, g);)
+  if (kh == 3 && kw == 3) {
+    DISPATCH_T(dtype, maxpool3x3_fwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, g);)
+  } else {
+    DISPATCH_T(dtype, maxpool_fwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, g);)
+  }
   MPB_CHECK_LAUNCH();
   return 0;
 }
@@ -301,7 +436,13 @@ MPB_API int mpb_maxpool_bwd(const void* dy, const unsigned char* idx, void* dx, 
   if (C % 8 != 0) return -1;
   const PoolGeom g = geom(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw);
   const long long total = (long long)N * H * W * (C / 8);
-  DISPATCH_T(dtype, maxpool_bwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)dy, idx, (T*)dx, g);)
+  if (kh == 3 && kw == 3 && sh == 2 && sw == 2 && ph == 1 && pw == 1 && H % 2 == 0 && W % 2 == 0 && Ho == H / 2 &&
+      Wo == W / 2) {
+    const long long quads = (long long)N * Ho * Wo * (C / 8);
+    DISPATCH_T(dtype, maxpool3x3s2_bwd_kernel<T><<<grid_for(quads, 256), 256, 0, (cudaStream_t)stream>>>((const T*)dy, idx, (T*)dx, g);)
+  } else {
+    DISPATCH_T(dtype, maxpool_bwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)dy, idx, (T*)dx, g);)
+  }
   MPB_CHECK_LAUNCH();
   return 0;
 }

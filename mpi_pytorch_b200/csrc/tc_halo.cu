@@ -416,6 +416,30 @@ void pick_tile(int Ho, int Wo, int S, int* TR, int* TW) {
   }
 }
 
+// Can the persistent, weights-resident variant run this layer, and with which tile width?  Prefers BN = 128 and
+// falls back to two 64-wide passes when only half of the filter bank fits (activation tiles are then fetched twice,
+// which is still far less traffic than streaming weights per tap).
+bool plan_persistent(int Ci, int Co, int R, int S, int Ho, int Wo, int* BN_out, int* a_stages_out) {
+  int TR, TW;
+  pick_tile(Ho, Wo, S, &TR, &TW);
+  const int pitch = TW + S - 1, box_h = TR + R - 1;
+  if (pitch > 256 || box_h > 256) return false;
+  const int cblocks = (Ci + BK - 1) / BK;
+  if (cblocks > 2) return false;
+  const long long a_stage = ((long long)box_h * pitch * 128 + 1023) / 1024 * 1024;
+  const int first = (Co > 64) ? 128 : 64;
+  for (int BN = first; BN >= 64; BN -= 64) {
+    const long long wbytes = (long long)cblocks * R * S * BN * BK * 2;
+    const long long room = 208 * 1024 - 2048 - wbytes;
+    if (room >= 2 * a_stage) {
+      int st = (int)(room / a_stage);
+      *BN_out = BN; *a_stages_out = st > 4 ? 4 : st;
+      return true;
+    }
+  }
+  return false;
+}
+
 int launch_halo(const void* in, const void* w, void* out, const float* bias, float* stats, int N, int Hi, int Wi, int Ci,
                 int Ho, int Wo, int Co, int R, int S, int ph, int pw, int b_mn, int flip, int w_rows, long long w_cols_total,
                 int w_cols, cudaStream_t st) {
@@ -428,6 +452,9 @@ int launch_halo(const void* in, const void* w, void* out, const float* bias, flo
   p.pitch = p.TW + S - 1;
   p.tiles_h = (Ho + p.TR - 1) / p.TR; p.tiles_w = (Wo + p.TW - 1) / p.TW;
   p.BN = (Co > 64) ? 128 : 64; p.b_mn = b_mn; p.flip = flip; p.w_cols = w_cols;
+  int bn_p = 0, a_st_p = 0;
+  const bool persistent = env_int("MPB_HALO_PERSIST", 1) != 0 && plan_persistent(Ci, Co, R, S, Ho, Wo, &bn_p, &a_st_p);
+  if (persistent) p.BN = bn_p;
   p.idesc = make_idesc(p.BN, 0, b_mn);
   const int box_h = p.TR + R - 1;
   if (p.pitch > 256 || box_h > 256) return -2;
@@ -455,25 +482,19 @@ int launch_halo(const void* in, const void* w, void* out, const float* bias, flo
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
-  // persistent, weights-resident variant when the CTA's filter bank fits beside a >= 2-deep activation ring
-  {
+  if (persistent) {
     const int cblocks = (Ci + BK - 1) / BK;
     const long long wbytes = (long long)cblocks * R * S * p.b_stage_bytes;
-    const long long room = 208 * 1024 - 2048 - wbytes;
-    int a_st = (int)(room / p.a_stage_bytes);
-    if (a_st > 4) a_st = 4;
     const int n_tiles_y = (Co + p.BN - 1) / p.BN;
-    if (env_int("MPB_HALO_PERSIST", 1) != 0 && a_st >= 2 && cblocks <= 2) {
-      p.a_stages = a_st;
-      const int smem_p = p.a_stages * p.a_stage_bytes + (int)wbytes + 2048;
-      const int num_tiles = N * p.tiles_h * p.tiles_w;
-      int ctas = kSMs / n_tiles_y;
-      if (ctas < 1) ctas = 1;
-      if (ctas > num_tiles) ctas = num_tiles;
-      dim3 gridp((unsigned)ctas, (unsigned)n_tiles_y, 1);
-      tc_halo_persist_kernel<<<gridp, kThreads, smem_p, st>>>(ta, tb, p, num_tiles);
-      return (int)cudaGetLastError();
-    }
+    p.a_stages = a_st_p;
+    const int smem_p = p.a_stages * p.a_stage_bytes + (int)wbytes + 2048;
+    const int num_tiles = N * p.tiles_h * p.tiles_w;
+    int ctas = kSMs / n_tiles_y;
+    if (ctas < 1) ctas = 1;
+    if (ctas > num_tiles) ctas = num_tiles;
+    dim3 gridp((unsigned)ctas, (unsigned)n_tiles_y, 1);
+    tc_halo_persist_kernel<<<gridp, kThreads, smem_p, st>>>(ta, tb, p, num_tiles);
+    return (int)cudaGetLastError();
   }
   dim3 grid((unsigned)(N * p.tiles_h * p.tiles_w), (unsigned)((Co + p.BN - 1) / p.BN), 1);
   tc_halo_kernel<<<grid, kThreads, smem, st>>>(ta, tb, p);
@@ -485,16 +506,8 @@ int launch_halo(const void* in, const void* w, void* out, const float* bias, flo
 // 1 when the persistent, weights-resident variant applies (the CTA's whole filter bank fits in shared memory beside
 // a >= 2-deep halo ring); that is the variant that beats the im2col kernel, the streaming one does not (measured).
 MPB_API int mpb_tc_halo_persistent_ok(int Ci, int Co, int R, int S, int Ho, int Wo) {
-  int TR, TW;
-  pick_tile(Ho, Wo, S, &TR, &TW);
-  const int pitch = TW + S - 1, box_h = TR + R - 1;
-  if (pitch > 256 || box_h > 256) return 0;
-  const int BN = (Co > 64) ? 128 : 64;
-  const int cblocks = (Ci + BK - 1) / BK;
-  const long long a_stage = ((long long)box_h * pitch * 128 + 1023) / 1024 * 1024;
-  const long long wbytes = (long long)cblocks * R * S * BN * BK * 2;
-  const long long room = 208 * 1024 - 2048 - wbytes;
-  return (cblocks <= 2 && room / a_stage >= 2) ? 1 : 0;
+  int bn = 0, st = 0;
+  return plan_persistent(Ci, Co, R, S, Ho, Wo, &bn, &st) ? 1 : 0;
 }
 
 // Fraction of the 128 GEMM rows that are real output pixels for this geometry (the caller's go / no-go signal).

@@ -22,6 +22,7 @@ import torch
 import torch.nn as nn
 
 from .. import ops
+from ..ops import scratch
 from ..data.synthetic import SyntheticShard
 from ..models import initialize_model
 from ..parallel import bootstrap
@@ -136,11 +137,25 @@ class Trainer:
 
     def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         """fwd -> CE -> zero_grad -> backward (buckets reduce+update as they complete) -> join."""
-        loss = self.forward_loss(images, labels)
-        self.optimizer.zero_grad()
-        loss.backward()
-        self.optimizer.step()
+        pool = self._scratch_pool()
+        if pool is not None:
+            scratch.arm(pool)          # one zeroing launch serves every BN-statistics / BN-backward accumulator
+        try:
+            loss = self.forward_loss(images, labels)
+            self.optimizer.zero_grad()
+            loss.backward()
+            self.optimizer.step()
+        finally:
+            if pool is not None:
+                scratch.disarm()
         return loss.detach()
+
+    def _scratch_pool(self):
+        if self.device.type != "cuda" or not getattr(self.s, "NATIVE_OPS", False):
+            return None
+        if getattr(self, "_scratch_buf", None) is None:
+            self._scratch_buf = scratch.new_buffer(self.device)
+        return self._scratch_buf
 
     # ------------------------------------------------------------------ CUDA-graph replay of the whole step
     def graph_capable(self) -> bool:

@@ -18,6 +18,8 @@ from typing import Optional, Tuple
 import torch
 import torch.nn.functional as F
 
+from . import scratch as _scratch
+
 from ..build import lib_path
 
 _LIB = ctypes.CDLL(lib_path())
@@ -200,7 +202,7 @@ def linear(x, w, b):
 # =============================================================================== batch norm (+add +relu)
 class _BNActFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, run_mean, run_var, eps, momentum, relu, training, sums):
+    def forward(ctx, x, gamma, beta, residual, run_mean, run_var, eps, momentum, relu, training, sums, nbt=None):
         x = _nhwc(x)
         n, c, h, w = x.shape
         m = n * h * w
@@ -212,9 +214,14 @@ class _BNActFn(torch.autograd.Function):
         if training and sums is None:
             sums = torch.empty(2 * c, dtype=torch.float32, device=dev)
             _call("mpb_bn_stats", _p(x), _p(sums), c_ll(m), c_int(c), c_int(_dt(x)), c_void_p(_stream()), launches=2)
-        _call("mpb_bn_fwd_apply", _p(x), _p(res), _p(out), _p(sums), _p(gamma), _p(beta), _p(run_mean), _p(run_var),
-              _p(save_mean), _p(save_invstd), c_ll(m), c_int(c), c_float(eps), c_float(momentum), c_int(int(relu)),
-              c_int(int(training)), c_int(_dt(x)), c_void_p(_stream()))
+        _call("mpb_bn_fwd_apply_ex", _p(x), _p(res), _p(out), _p(sums), _p(gamma), _p(beta), _p(run_mean), _p(run_var),
+              _p(save_mean), _p(save_invstd), _p(nbt), c_ll(m), c_int(c), c_float(eps), c_float(momentum),
+              c_int(int(relu)), c_int(int(training)), c_int(_dt(x)), c_void_p(_stream()))
+        # affine gradients go straight into the DP engine's gradient arena when the parameters live there
+        ctx.direct = None
+        if (gamma is not None and beta is not None and getattr(gamma, "_mpb_grad_ready", None) is not None
+                and getattr(beta, "_mpb_grad_ready", None) is not None):
+            ctx.direct = (gamma, beta)
         # BN -> ReLU without a residual: backward recomputes the mask from x, so `out` need not be kept for it
         recompute = bool(relu) and residual is None and training and beta is not None
         ctx.save_for_backward(x, None if recompute else out, gamma, beta if recompute else None, save_mean, save_invstd)
@@ -231,22 +238,36 @@ class _BNActFn(torch.autograd.Function):
         if gz.dtype != x.dtype:
             gz = gz.to(x.dtype)
         dx = torch.empty_like(x)
-        if out is None:                                   # recompute-mask variant: reads dz and x only
-            dsum = torch.empty(2 * c, dtype=torch.float32, device=x.device)
+        dsum, pooled = _scratch.take(2 * c, x.device)
+        direct = None
+        if ctx.direct is not None:
+            gp, bp = ctx.direct
+            if all(t.grad is not None and t.grad.dtype == torch.float32 and t.grad.is_contiguous() for t in (gp, bp)):
+                direct = (gp, bp)
+        if direct is not None:
+            dgamma, dbeta, acc = direct[0].grad, direct[1].grad, 1
+        else:
             dgamma = torch.empty(c, dtype=torch.float32, device=x.device)
             dbeta = torch.empty(c, dtype=torch.float32, device=x.device)
-            _call("mpb_bn_relu_bwd_recompute", _p(gz), _p(x), _p(gamma), _p(beta), _p(save_mean), _p(save_invstd), _p(dsum),
-                  _p(dx), _p(dgamma), _p(dbeta), c_ll(m), c_int(c), c_int(_dt(x)), c_void_p(_stream()), launches=3)
-            return dx, dgamma, dbeta, None, None, None, None, None, None, None, None
-        dres = torch.empty_like(x) if has_res else None
-        dsum = torch.empty(2 * c, dtype=torch.float32, device=x.device)
-        dgamma = torch.empty(c, dtype=torch.float32, device=x.device)
-        dbeta = torch.empty(c, dtype=torch.float32, device=x.device)
-        _call("mpb_bn_bwd", _p(gz), _p(out), _p(x), _p(gamma), _p(save_mean), _p(save_invstd), _p(dsum), _p(dx), _p(dres),
-              _p(dgamma), _p(dbeta), c_ll(m), c_int(c), c_int(int(relu)), c_int(_dt(x)), c_void_p(_stream()), launches=3)
-        if has_res and not relu:
-            dres = gz
-        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None
+            acc = 0
+        acc |= 2          # dsum is zero already (pool slice or fresh torch.zeros)
+        dres = None
+        if out is None:                                   # recompute-mask variant: reads dz and x only
+            _call("mpb_bn_relu_bwd_recompute_ex", _p(gz), _p(x), _p(gamma), _p(beta), _p(save_mean), _p(save_invstd),
+                  _p(dsum), _p(dx), _p(dgamma), _p(dbeta), c_ll(m), c_int(c), c_int(acc), c_int(_dt(x)),
+                  c_void_p(_stream()), launches=2)
+        else:
+            dres = torch.empty_like(x) if has_res else None
+            _call("mpb_bn_bwd_ex", _p(gz), _p(out), _p(x), _p(gamma), _p(save_mean), _p(save_invstd), _p(dsum), _p(dx),
+                  _p(dres), _p(dgamma), _p(dbeta), c_ll(m), c_int(c), c_int(int(relu)), c_int(acc), c_int(_dt(x)),
+                  c_void_p(_stream()), launches=2)
+            if has_res and not relu:
+                dres = gz
+        if direct is not None:
+            for t in direct:
+                t._mpb_grad_ready(t)
+            dgamma = dbeta = None
+        return dx, dgamma, dbeta, dres, None, None, None, None, None, None, None, None
 
 
 def bn_stats(y: torch.Tensor) -> torch.Tensor:
@@ -269,10 +290,13 @@ def batch_norm_act(x, bn, residual=None, relu=False, sums=None):
         _note_fallback("batch_norm")
         return ref.batch_norm_act(x, bn, residual, relu)
     momentum = 0.1 if bn.momentum is None else float(bn.momentum)
-    if bn.training:
-        bn.num_batches_tracked.add_(1)
+    nbt = bn.num_batches_tracked
+    if nbt is not None and not (nbt.is_cuda and nbt.dtype == torch.int64):
+        if bn.training:
+            nbt.add_(1)
+        nbt = None
     return _BNActFn.apply(x, bn.weight, bn.bias, residual, bn.running_mean, bn.running_var, float(bn.eps), momentum,
-                          bool(relu), bool(bn.training), sums)
+                          bool(relu), bool(bn.training), sums, nbt)
 
 
 def conv_bn_act(x, conv, bn, relu=True, residual=None):

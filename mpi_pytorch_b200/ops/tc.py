@@ -13,6 +13,7 @@ from typing import Optional, Tuple
 
 import torch
 
+from . import scratch as _scratch
 from ..build import lib_path
 
 ENABLED = os.environ.get("MPB_TC", "1").lower() not in ("0", "false", "off")
@@ -134,7 +135,7 @@ def halo_ok(out_h: int, out_w: int, r: int, s: int, stride, ci: int = 0, co: int
 def conv_fprop(x, w, bias, stride, padding, want_stats=False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     n, c, h, wd, k, r, s, p, q = _geom(x.shape, w.shape, stride, padding)
     y = torch.empty((n, k, p, q), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
-    stats = torch.zeros(2 * k, dtype=torch.float32, device=x.device) if want_stats else None
+    stats = _scratch.take(2 * k, x.device)[0] if want_stats else None
     if halo_ok(p, q, r, s, stride, c, k):
         rc = _LIB.mpb_tc_conv_fprop_halo(_p(x), _p(w), _p(y), _p(None if bias is None else bias.float()), _p(stats),
                                          c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r), c_int(s), c_int(p),
@@ -233,7 +234,7 @@ def conv_fprop_im2col(x, w, bias, stride, padding, want_stats=False):
     xcol = im2col(x, w.shape, stride, padding)
     wmat = torch.zeros((k, kp), dtype=torch.bfloat16, device=x.device)
     wmat[:, : c * r * s] = w.permute(0, 2, 3, 1).reshape(k, c * r * s)          # KRSC flattened
-    stats = torch.zeros(2 * k, dtype=torch.float32, device=x.device) if want_stats else None
+    stats = _scratch.take(2 * k, x.device)[0] if want_stats else None
     y2d = gemm(xcol, wmat, n * p * q, k, kp, False, False, None if bias is None else bias.float(), stats=stats)
     y = y2d.view(n, p, q, k).permute(0, 3, 1, 2)                                  # logical NCHW, physical NHWC
     return y, stats, xcol

@@ -25,10 +25,19 @@ def main():
         tr.train_step(*batches[i % 2])
     torch.cuda.synchronize()
     from torch.profiler import ProfilerActivity, profile
-    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+    want_aten = os.environ.get("MPB_PROF_ATEN", "0") == "1"
+    acts = [ProfilerActivity.CUDA] + ([ProfilerActivity.CPU] if want_aten else [])
+    with profile(activities=acts, record_shapes=want_aten) as prof:
         for i in range(steps):
             tr.train_step(*batches[i % 2])
         torch.cuda.synchronize()
+    if want_aten:      # which framework ops still launch library elementwise kernels (targets for fusion)
+        ops = collections.Counter()
+        for ev in prof.events():
+            if ev.device_type == torch.autograd.DeviceType.CPU and ev.name.startswith("aten::"):
+                ops[(ev.name, str(ev.input_shapes)[:80])] += 1
+        for (name, shp), n in ops.most_common(40):
+            print("aten {:6.1f}x  {:28s} {}".format(n / steps, name, shp))
     agg = collections.defaultdict(lambda: [0, 0.0])
     for ev in prof.events():
         if ev.device_type == torch.autograd.DeviceType.CUDA:

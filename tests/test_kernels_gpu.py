@@ -103,6 +103,22 @@ def test_maxpool(dtype, tol, k, s, p, ceil):
     assert torch.allclose(x.grad.float(), xr.grad, atol=tol * 4)
 
 
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-6), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("hw", [(28, 28), (12, 30)])
+def test_maxpool_stem_quad_backward(dtype, tol, hw):
+    """3x3/s2/p1 on even H, W takes the one-thread-per-2x2-quad backward kernel (stem pool of ResNet/DenseNet)."""
+    torch.manual_seed(5)
+    x = cl(F.relu(torch.randn(3, 64, *hw, device="cuda")).to(dtype)).requires_grad_(True)
+    y = nat().max_pool2d(x, 3, 2, 1, False)
+    g = cl(torch.randn_like(y))
+    y.backward(g)
+    xr = x.detach().float().requires_grad_(True)
+    yr = F.max_pool2d(xr, 3, 2, 1)
+    yr.backward(g.float())
+    assert torch.allclose(y.float(), yr, atol=tol)
+    assert torch.allclose(x.grad.float(), xr.grad, atol=tol * 4)
+
+
 @pytest.mark.parametrize("k,s,p,ceil,cip", [(2, 2, 0, False, True), (3, 1, 1, False, True), (5, 3, 0, False, True),
                                             (3, 2, 1, True, False)])
 def test_avgpool(k, s, p, ceil, cip):
