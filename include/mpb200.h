@@ -123,6 +123,12 @@ int mpb_tc_conv_dgrad_strided(const void* dy, const void* w, void* dx, int N, in
 /* dw[K,R,S,C] (fp32) += split-K partial sums; dw must hold zeros or a partial gradient to accumulate into.     */
 int mpb_tc_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R, int S,
                       int P, int Q, int stride, int pad_h, int pad_w, int dil, int splitk, void* stream);
+/* Persistent halo-tile wgrad for stride-1, dilation-1 filters larger than 1x1 (tc_wgrad_halo.cu): same contract
+ * as mpb_tc_conv_wgrad.  mpb_tc_wgrad_halo_ok says whether a layer fits it (C == 64 or C % 128 == 0, K % 64 == 0,
+ * accumulators within 512 TMEM columns, a >= 2-stage ring within shared memory); -2 otherwise.                   */
+int mpb_tc_wgrad_halo_ok(int C, int K, int R, int S, int Ho, int Wo);
+int mpb_tc_conv_wgrad_halo(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R, int S,
+                           int P, int Q, int pad_h, int pad_w, void* stream);
 
 /* ---- K1 / K2 / K13 peer-memory collectives over NVLink (mpi_tools.py:30-37,47-53; evaluation_pipeline.py:196)
  * Symmetric buffers: cudaMalloc on every rank, handles exchanged by the caller, mapped with the ipc helpers.

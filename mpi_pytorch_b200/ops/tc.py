@@ -132,6 +132,17 @@ def halo_ok(out_h: int, out_w: int, r: int, s: int, stride, ci: int = 0, co: int
     return bool(_LIB.mpb_tc_halo_persistent_ok(c_int(ci), c_int(co), c_int(r), c_int(s), c_int(out_h), c_int(out_w)))
 
 
+WGRAD_HALO = os.environ.get("MPB_TC_WGRAD_HALO", "1") != "0"
+
+
+def wgrad_halo_ok(c: int, k: int, r: int, s: int, out_h: int, out_w: int, stride) -> bool:
+    """Stride-1 filters larger than 1x1 with C == 64 or C % 128 == 0 (and K % 64 == 0) take the persistent halo-tile
+    weight-gradient kernel (tc_wgrad_halo.cu): x tile fetched once per filter row instead of once per tap."""
+    if not WGRAD_HALO or stride[0] != 1 or stride[1] != 1 or r * s == 1:
+        return False
+    return bool(_LIB.mpb_tc_wgrad_halo_ok(c_int(c), c_int(k), c_int(r), c_int(s), c_int(out_h), c_int(out_w)))
+
+
 def conv_fprop(x, w, bias, stride, padding, want_stats=False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     n, c, h, wd, k, r, s, p, q = _geom(x.shape, w.shape, stride, padding)
     y = torch.empty((n, k, p, q), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
@@ -181,6 +192,13 @@ def conv_wgrad(gy, x, w_shape, stride, padding, out: Optional[torch.Tensor] = No
     atomically accumulated straight into it -- no temporary, no separate add."""
     n, c, h, wd, k, r, s, p, q = _geom(x.shape, w_shape, stride, padding)
     dw = torch.zeros((k, r, s, c), dtype=torch.float32, device=gy.device) if out is None else out
+    if wgrad_halo_ok(c, k, r, s, p, q, stride):
+        rc = _LIB.mpb_tc_conv_wgrad_halo(_p(gy), _p(x), _p(dw), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k),
+                                         c_int(r), c_int(s), c_int(p), c_int(q), c_int(padding[0]), c_int(padding[1]),
+                                         c_void_p(_stream()))
+        LAUNCHES["n"] += 2 if out is None else 1
+        _check(rc, "mpb_tc_conv_wgrad_halo")
+        return out if out is not None else dw.permute(0, 3, 1, 2)
     bn = 128 if c > 64 else 64
     tiles = ((k + 127) // 128) * r * s * ((c + bn - 1) // bn)
     num_kb = (n * p * q + 63) // 64

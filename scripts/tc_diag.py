@@ -19,6 +19,9 @@ GEMM_CASES = {
     "gemm_tn_k256": (128, 128, 256, 0, 0),
     "gemm_tn_head": (256, 1000, 512, 0, 0),
     "gemm_tn_big": (4096, 4096, 4096, 0, 0),
+    "big_a_mn": (4096, 4096, 4096, 1, 0),      # operand-majorness sweep at a compute-bound size
+    "big_b_mn": (4096, 4096, 4096, 0, 1),
+    "big_ab_mn": (4096, 4096, 4096, 1, 1),
     "gemm_bmn": (256, 512, 1000, 0, 1),        # linear dX shape
     "gemm_amn_bmn": (1000, 512, 256, 1, 1),    # linear dW shape
     "gemm_amn_bmn_small": (128, 64, 64, 1, 1),

@@ -45,7 +45,19 @@ CONVS = [(2, 64, 8, 8, 64, 1, 1, 0), (2, 64, 8, 8, 64, 3, 1, 1), (8, 64, 56, 56,
          (4, 96, 12, 12, 48, 3, 1, 1), (4, 16, 13, 13, 64, 1, 1, 0), (2, 160, 9, 9, 192, 3, 1, 1),
          (2, 288, 17, 17, 384, 3, 2, 0), (2, 80, 10, 10, 192, 3, 1, 0),
          # more strided shapes: odd sizes, 5x5 stride 2, stride 3, 1x1 stride 2 on odd maps
-         (2, 64, 15, 15, 64, 5, 2, 2), (2, 64, 20, 20, 64, 3, 3, 1), (2, 64, 9, 9, 128, 1, 2, 0), (2, 64, 14, 14, 64, 7, 2, 3)]
+         (2, 64, 15, 15, 64, 5, 2, 2), (2, 64, 20, 20, 64, 3, 3, 1), (2, 64, 9, 9, 128, 1, 2, 0), (2, 64, 14, 14, 64, 7, 2, 3),
+         # halo-tile wgrad: row mode with one / several channel and k blocks, wide and short maps, many images per CTA
+         (2, 128, 10, 10, 128, 3, 1, 1), (3, 128, 6, 40, 64, 3, 1, 1), (40, 256, 7, 7, 128, 3, 1, 1),
+         (37, 64, 28, 28, 64, 3, 1, 1)]
+
+
+def test_wgrad_halo_kernel_covers_the_resnet_layers():
+    tc = _tc()
+    for (c, k, hw) in ((64, 64, 56), (128, 128, 28), (256, 256, 14), (512, 512, 7)):
+        assert tc.wgrad_halo_ok(c, k, 3, 3, hw, hw, (1, 1))
+    assert not tc.wgrad_halo_ok(64, 128, 3, 3, 28, 28, (2, 2))      # strided: im2col-mode kernel
+    assert not tc.wgrad_halo_ok(64, 64, 1, 1, 56, 56, (1, 1))       # 1x1: plain GEMM
+    assert not tc.wgrad_halo_ok(96, 48, 3, 3, 12, 12, (1, 1))       # ragged channel counts: im2col-mode kernel
 
 
 def test_conv_rect_kernels_inception():
