@@ -269,6 +269,7 @@ def run_ours(args) -> None:
                        "l2": "per-step working set (activations, ~GBs) >> 126 MB L2; 4 input batches rotate; no explicit flush",
                        "device": str(dev), "allreduce": getattr(tr.engine.coll, "name", "?"),
                        "native_ops": bool(cuda and ops.native_enabled()), "library_fallbacks": fb,
+                       "scratch_pool": dict(__import__("mpi_pytorch_b200.ops.scratch", fromlist=["stats"]).stats),
                        "final_loss": final_loss, "host_enqueue_ms_per_step": host_enqueue_ms,
                        "cuda_graph": bool(use_graph)},
             "clocks": {k: clocks.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons")},

@@ -228,6 +228,7 @@ bool plan_wgrad(int C, int K, int R, int S, int Ho, int Wo, WgParams* out) {
   if (best < 0) return false;
   p.kgroups = (K + p.BNk - 1) / p.BNk;
   p.rgroups = p.pair ? 1 : R;
+  if ((p.pair ? 1 : C / 128) * p.kgroups * p.rgroups > env_int("MPB_WG_MAX_Y", 40)) return false;   // few pixel groups per column group: tc_gemm.cu's split-K form is faster (l4)
   for (int j = 0; j < p.njobs; ++j) {
     if (p.pair) {
       const int t0 = 2 * j, t1 = t0 + 1;
