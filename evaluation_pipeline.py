@@ -69,8 +69,12 @@ def pipeline(world=None, settings=None, n_samples=None):
                 model = model.to(torch.bfloat16)
         return model
     dtype = torch.bfloat16 if (world.device.type == 'cuda' and settings.DTYPE == 'bf16') else torch.float32
+    coll = None
+    if world.device.type == 'cuda' and world.size > 1:
+        from mpi_pytorch_b200.parallel.collectives import make_collectives
+        coll = make_collectives(world, settings.ALLREDUCE_ALGO)     # final count: mpb_count_allreduce over NVLink
     pipe = EvalPipeline(world, n, raw_hw, (settings.HEIGHT, settings.WIDTH), source, labels, model_fn,
-                        micro_batch=settings.PIPE_MICROBATCH, seed=settings.SEED, dtype=dtype)
+                        micro_batch=settings.PIPE_MICROBATCH, seed=settings.SEED, dtype=dtype, collectives=coll)
     return pipe.run()
 
 

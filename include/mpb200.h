@@ -81,6 +81,10 @@ int mpb_adaptive_avgpool(const void* in, void* out, int N, int H, int W, int C, 
 int mpb_relu_fwd(const void* x, void* y, long long n, int dtype, void* stream);
 int mpb_relu_bwd(const void* dy, const void* y, void* dx, long long n, int dtype, void* stream);
 int mpb_dropout(const void* x, void* y, long long n, unsigned int seed, float p, int dtype, void* stream);
+/* `epoch` (nullable device pointer): a step counter mixed into the seed on the device, so a captured launch draws a
+ * new mask on every CUDA-graph replay; the backward call of the same step passes the same pointer and seed.      */
+int mpb_dropout_ex(const void* x, void* y, long long n, unsigned int seed, const long long* epoch, float p, int dtype,
+                   void* stream);
 
 /* ---- K9 resize + normalise, K14 synthetic data (main.py:62-65, evaluation_pipeline.py:89,116-122) ---------
  * mode 0: u8 -> u8 NHWC; 1: u8 -> normalised float via a u8 rounding (PIL semantics); 2: u8 -> float directly. */

@@ -393,7 +393,11 @@ __global__ void __launch_bounds__(256) relu_bwd_kernel(const T* __restrict__ dy,
 // y = x * keep/(1-p) with keep = hash(seed, i) >= p*2^32 ; the same call with the same seed on dy is the backward.
 template <typename T>
 __global__ void __launch_bounds__(256) dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long long n8,
-                                                      uint32_t seed, uint32_t thresh, float scale) {
+                                                      uint32_t seed, uint32_t thresh, float scale,
+                                                      const long long* __restrict__ epoch) {
+  // `epoch` (nullable): a device-resident step counter mixed into the seed, so a CUDA-graph replay of the same launch
+  // draws a fresh mask every step while forward and backward of one step still agree
+  if (epoch) seed ^= hash32((uint32_t)(*epoch) * 0x85EBCA6Bu + 0x27D4EB2Fu);
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
     float v[8];
     load8(x + i * 8, v);
@@ -480,12 +484,16 @@ MPB_API int mpb_relu_bwd(const void* dy, const void* y, void* dx, long long n, i
   MPB_CHECK_LAUNCH();
   return 0;
 }
-MPB_API int mpb_dropout(const void* x, void* y, long long n, unsigned int seed, float p, int dtype, void* stream) {
+MPB_API int mpb_dropout_ex(const void* x, void* y, long long n, unsigned int seed, const long long* epoch, float p,
+                           int dtype, void* stream) {
   if (n % 8 != 0) return -1;
   const double t = (double)p * 4294967296.0;
   const uint32_t thresh = t >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)t;
   const float scale = p < 1.f ? 1.f / (1.f - p) : 0.f;
-  DISPATCH_T(dtype, dropout_kernel<T><<<grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, n / 8, seed, thresh, scale);)
+  DISPATCH_T(dtype, dropout_kernel<T><<<grid_for(n / 8, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, n / 8, seed, thresh, scale, epoch);)
   MPB_CHECK_LAUNCH();
   return 0;
+}
+MPB_API int mpb_dropout(const void* x, void* y, long long n, unsigned int seed, float p, int dtype, void* stream) {
+  return mpb_dropout_ex(x, y, n, seed, nullptr, p, dtype, stream);
 }

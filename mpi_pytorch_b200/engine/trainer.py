@@ -140,6 +140,8 @@ class Trainer:
         pool = self._scratch_pool()
         if pool is not None:
             scratch.arm(pool)          # one zeroing launch serves every BN-statistics / BN-backward accumulator
+            if self._has_dropout:
+                ops.native().advance_dropout_epoch(self.device)     # fresh masks on every CUDA-graph replay
         try:
             loss = self.forward_loss(images, labels)
             self.optimizer.zero_grad()
@@ -159,10 +161,16 @@ class Trainer:
 
     # ------------------------------------------------------------------ CUDA-graph replay of the whole step
     def graph_capable(self) -> bool:
-        """Whole-step capture needs a CUDA device, fixed shapes and no host-seeded randomness (Dropout)."""
-        if self.device.type != "cuda":
-            return False
-        return not any(isinstance(m, nn.Dropout) and m.p > 0 for m in self.model.modules())
+        """Whole-step capture needs a CUDA device and fixed shapes.  Dropout is capturable on the native path: its
+        kernels mix a device-resident step counter into the seed (``advance_dropout_epoch``); on the torch-ops path
+        the masks come from torch's graph-aware CUDA generator."""
+        return self.device.type == "cuda"
+
+    @property
+    def _has_dropout(self) -> bool:
+        if getattr(self, "_has_dropout_cached", None) is None:
+            self._has_dropout_cached = any(isinstance(m, nn.Dropout) and m.p > 0 for m in self.model.modules())
+        return self._has_dropout_cached
 
     def train_step_graphed(self, images: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         """Same work as :meth:`train_step`, but forward + backward + bucketed all-reduce + fused Adam are

@@ -345,11 +345,28 @@ def relu(x, inplace=False):
 _DROP_SEED = itertools.count(0x5EED)
 
 
+_DROP_EPOCH = {}      # device -> int64[1] step counter mixed into every dropout seed ON THE DEVICE
+
+
+def dropout_epoch(device) -> torch.Tensor:
+    dev = torch.device(device)
+    if dev not in _DROP_EPOCH:
+        _DROP_EPOCH[dev] = torch.zeros(1, dtype=torch.int64, device=dev)
+    return _DROP_EPOCH[dev]
+
+
+def advance_dropout_epoch(device) -> None:
+    """One launch per training step (captured with it): replays of a CUDA graph then draw fresh dropout masks even
+    though the host-side seeds were frozen at capture time."""
+    dropout_epoch(device).add_(1)
+
+
 class _DropoutFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, p, seed):
         y = torch.empty_like(x)
-        _call("mpb_dropout", _p(x), _p(y), c_ll(x.numel()), ctypes.c_uint(seed), c_float(p), c_int(_dt(x)),
+        ep = dropout_epoch(x.device)
+        _call("mpb_dropout_ex", _p(x), _p(y), c_ll(x.numel()), ctypes.c_uint(seed), _p(ep), c_float(p), c_int(_dt(x)),
               c_void_p(_stream()))
         ctx.conf = (p, seed)
         return y
@@ -359,8 +376,9 @@ class _DropoutFn(torch.autograd.Function):
         p, seed = ctx.conf
         gy = gy.contiguous()
         dx = torch.empty_like(gy)
-        _call("mpb_dropout", _p(gy), _p(dx), c_ll(gy.numel()), ctypes.c_uint(seed), c_float(p), c_int(_dt(gy)),
-              c_void_p(_stream()))
+        ep = dropout_epoch(gy.device)
+        _call("mpb_dropout_ex", _p(gy), _p(dx), c_ll(gy.numel()), ctypes.c_uint(seed), _p(ep), c_float(p),
+              c_int(_dt(gy)), c_void_p(_stream()))
         return dx, None, None
 
 

@@ -91,8 +91,9 @@ class EvalPipeline:
     def __init__(self, world, n_samples: int, raw_hw: Tuple[int, int], out_hw: Tuple[int, int],
                  source: Callable[[int, int], torch.Tensor], labels: torch.Tensor,
                  model_fn: Callable[[], torch.nn.Module], micro_batch: int = 32, seed: int = 0,
-                 dtype: torch.dtype = torch.float32, resize_mode: str = "bicubic"):
+                 dtype: torch.dtype = torch.float32, resize_mode: str = "bicubic", collectives=None):
         self.w = world
+        self.coll = collectives        # optional: sums the per-rank counts with the peer-memory count kernel (K13)
         self.dev = world.device
         self.roles = assign_roles(world.size)
         self.n, self.mb, self.seed = int(n_samples), int(micro_batch), seed
@@ -226,7 +227,10 @@ class EvalPipeline:
             self.log.info("Finished node {}, acc {}".format(r, float(self.correct.item()) / max(self.n, 1)))
         total = self.correct.clone()
         if self.w.size > 1:
-            dist.all_reduce(total)                      # exact int64 count (C23 / K13)
+            if self.coll is not None:
+                self.coll.all_reduce_sum_i64(total)     # exact int64 count through peer memory (C23 / K13)
+            else:
+                dist.all_reduce(total)
         acc = float(total.item()) / max(self.n, 1)
         if r == 0:
             self.log.info("Accuracy is {}".format(acc))

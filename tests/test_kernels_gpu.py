@@ -158,6 +158,33 @@ def test_relu_and_dropout():
     assert torch.equal(z.grad, d.detach())
 
 
+def test_dropout_in_cuda_graph_draws_a_new_mask_per_replay():
+    """The dropout seed is mixed with a device-resident step counter, so a captured step is replayable."""
+    n = nat()
+    x = torch.ones(64 * 1024, device="cuda", requires_grad=True)
+    n.dropout_epoch(x.device)                       # the counter must exist before capture
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):                   # warm-up outside the graph
+        torch.autograd.grad(n.dropout(x, 0.5).sum(), x)
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        n.advance_dropout_epoch(x.device)
+        y = n.dropout(x, 0.5)
+        (gx,) = torch.autograd.grad(y.sum(), x)
+    masks = []
+    for _ in range(3):
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(y != 0, gx != 0)         # forward and backward of one replay agree
+        assert 0.45 < float((y != 0).float().mean()) < 0.55
+        assert torch.all(y[y != 0] == 2.0)
+        masks.append((y != 0).clone())
+    assert not torch.equal(masks[0], masks[1]) and not torch.equal(masks[1], masks[2])
+
+
 def test_adam_and_sgd_flat():
     from mpi_pytorch_b200.ops import reference as ref
     torch.manual_seed(3)
