@@ -11,6 +11,7 @@
 // Thread mapping: 8 channels per thread (16 B bf16 vectors), blockDim = cvecs * rows_per_block so a
 // thread keeps the same channel group for its whole row loop and can accumulate in registers.
 #include "common.cuh"
+#include "bn_stream.cuh"
 
 using namespace mpb;
 
@@ -223,6 +224,9 @@ MPB_API int mpb_bn_fwd_apply_ex(const void* x, const void* res, void* out, const
                                 float* save_invstd, long long* num_batches, long long M, int C, float eps,
                                 float momentum, int relu, int training, int dtype, void* stream) {
   if (C % 8 != 0 || C > 2048) return -1;
+  if (mpbbn::stream_ok(M, C, dtype))      // large bf16 tensors: bulk-copy streaming form (bn_stream.cu)
+    return mpbbn::stream_fwd(x, res, out, sums, gamma, beta, run_mean, run_var, save_mean, save_invstd, num_batches, M, C,
+                             eps, momentum, relu, training, (cudaStream_t)stream);
   const Map mp = make_map(C);
   const int grid = rows_grid(M, mp.rows_per_block, 8);
   DISPATCH_T(dtype, bn_fwd_apply_kernel<T><<<grid, mp.threads, 0, (cudaStream_t)stream>>>(
@@ -250,6 +254,9 @@ MPB_API int mpb_bn_bwd_ex(const void* dz, const void* z, const void* x, const fl
   cudaStream_t st = (cudaStream_t)stream;
   const int accumulate = flags & 1;
   if (!(flags & 2)) MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));
+  if (mpbbn::stream_ok(M, C, dtype))
+    return mpbbn::stream_bwd(dz, z, x, gamma, nullptr, save_mean, save_invstd, dsum, dx, dres, dgamma, dbeta, M, C,
+                             relu ? 1 : 0, accumulate, st);
   const Map mp = make_map(C);
   const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
   const int g1 = rows_grid(M, mp.rows_per_block, 4), g2 = rows_grid(M, mp.rows_per_block, 8);
@@ -361,6 +368,9 @@ MPB_API int mpb_bn_relu_bwd_recompute_ex(const void* dz, const void* x, const fl
   cudaStream_t st = (cudaStream_t)stream;
   const int accumulate = flags & 1;
   if (!(flags & 2)) MPB_CUDA(cudaMemsetAsync(dsum, 0, 2 * C * sizeof(float), st));
+  if (mpbbn::stream_ok(M, C, dtype))
+    return mpbbn::stream_bwd(dz, nullptr, x, gamma, beta, save_mean, save_invstd, dsum, dx, nullptr, dgamma, dbeta, M, C, 2,
+                             accumulate, st);
   const Map mp = make_map(C);
   const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
   const int g1 = rows_grid(M, mp.rows_per_block, 8), g2 = rows_grid(M, mp.rows_per_block, 8);

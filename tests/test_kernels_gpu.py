@@ -45,8 +45,20 @@ def test_count_correct():
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 3e-2)])
 @pytest.mark.parametrize("C,relu,res", [(64, True, False), (128, True, True), (288, False, False), (80, True, True)])
 def test_batchnorm_train_fwd_bwd(dtype, tol, C, relu, res):
+    _bn_case(dtype, tol, C, relu, res, 8, 14, 14)
+
+
+@pytest.mark.parametrize("C,relu,res,N,H,W", [(64, True, False, 35, 31, 31), (128, True, True, 16, 33, 33),
+                                              (256, False, False, 16, 24, 24), (512, True, True, 9, 23, 23),
+                                              (64, False, True, 43, 28, 28), (2048, True, False, 5, 15, 15)])
+def test_batchnorm_streaming_kernels(C, relu, res, N, H, W):
+    """bf16 tensors >= 4 MB take the bulk-copy streaming kernels (bn_stream.cu): ragged last chunks, every mask mode."""
+    assert N * H * W * C * 2 >= 4 << 20
+    _bn_case(torch.bfloat16, 3e-2, C, relu, res, N, H, W)
+
+
+def _bn_case(dtype, tol, C, relu, res, N, H, W):
     torch.manual_seed(1)
-    N, H, W = 8, 14, 14
     x = cl((torch.randn(N, C, H, W, device="cuda") * 2 + 0.5).to(dtype)).requires_grad_(True)
     r = cl(torch.randn(N, C, H, W, device="cuda").to(dtype)).requires_grad_(True) if res else None
     bn = nn.BatchNorm2d(C).cuda()
