@@ -130,6 +130,17 @@ int mpb_tc_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
 /* Persistent halo-tile wgrad for stride-1, dilation-1 filters larger than 1x1 (tc_wgrad_halo.cu): same contract
  * as mpb_tc_conv_wgrad.  mpb_tc_wgrad_halo_ok says whether a layer fits it (C == 64 or C % 128 == 0, K % 64 == 0,
  * accumulators within 512 TMEM columns, a >= 2-stage ring within shared memory); -2 otherwise.                   */
+/* Variants taking explicit element strides of x between pixels / rows / images; a pixel stride smaller than C
+ * describes overlapping super-pixels.  With mpb_s2d_stem (x NHWC, 4*C <= 16, H and W even -> out [N][H/2][Wp][16],
+ * lpad zero pixels on the left) a 7x7 stride-2 stem becomes a 4x1 stride-1 convolution with 64 channels:
+ * no im2col matrix (models.py:33,68,81 stems).                                                                  */
+int mpb_s2d_stem(const void* x, void* out, int N, int H, int W, int C, int Wp, int lpad, void* stream);
+int mpb_tc_conv_fprop_halo_strided(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H,
+                                   int W, int C, int K, int R, int S, int P, int Q, int pad_h, int pad_w,
+                                   long long xs_w, long long xs_h, long long xs_n, void* stream);
+int mpb_tc_conv_wgrad_halo_strided(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R,
+                                   int S, int P, int Q, int pad_h, int pad_w, long long xs_w, long long xs_h,
+                                   long long xs_n, void* stream);
 int mpb_tc_wgrad_halo_ok(int C, int K, int R, int S, int Ho, int Wo);
 int mpb_tc_conv_wgrad_halo(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R, int S,
                            int P, int Q, int pad_h, int pad_w, void* stream);

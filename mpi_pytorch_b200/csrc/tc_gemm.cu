@@ -596,3 +596,49 @@ MPB_API int mpb_im2col_nhwc(const void* x, void* out, int N, int H, int W, int C
   MPB_CHECK_LAUNCH();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// Space-to-depth for stride-2 stems with few input channels (7x7/2 on 3 channels: ResNet, DenseNet, SqueezeNet).
+//   out[n][h2][j][(b*2 + b')*C + c] = x[n][2*h2 + b][2*(j - lpad) + b'][c]      (16 elements per output pixel, zero tails)
+// with `lpad` zero pixels on the left and enough on the right that every window of 4 neighbouring pixels exists.
+// A 7x7/2 convolution then is a 4x4/1 convolution over 4*C channels; reading 4 neighbouring 16-element pixels as ONE
+// 64-element pixel (tensor map with a 16-element pixel stride) makes it a 4x1 stride-1 convolution with 64 channels,
+// which the halo-tile fprop / wgrad kernels run without any im2col matrix (976 MB per step for ResNet at batch 256).
+// ------------------------------------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) s2d_stem_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out,
+                                                       int N, int H, int W, int C, int H2, int Wp, int lpad) {
+  const long long total = (long long)N * H2 * Wp;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int j = (int)(i % Wp);
+    const long long t = i / Wp;
+    const int h2 = (int)(t % H2);
+    const int n = (int)(t / H2);
+    const int px = j - lpad;
+    __align__(16) __nv_bfloat16 v[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) v[e] = __float2bfloat16(0.f);
+    if (px >= 0 && 2 * px + 1 < W) {
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const __nv_bfloat16* src = x + (((long long)n * H + 2 * h2 + b) * W + 2 * px) * C;     // 2 pixels = 2*C contiguous
+        for (int e = 0; e < 2 * C; ++e) v[b * 2 * C + e] = src[e];
+      }
+    }
+    uint4* dst = reinterpret_cast<uint4*>(out + i * 16);
+    dst[0] = reinterpret_cast<const uint4*>(v)[0];
+    dst[1] = reinterpret_cast<const uint4*>(v)[1];
+  }
+}
+}  // namespace
+
+// x: NHWC bf16 [N][H][W][C] with 4*C <= 16, H and W even; out: [N][H/2][Wp][16] bf16.
+MPB_API int mpb_s2d_stem(const void* x, void* out, int N, int H, int W, int C, int Wp, int lpad, void* stream) {
+  if (4 * C > 16 || (H & 1) || (W & 1) || lpad + W / 2 > Wp) return -2;
+  const long long total = (long long)N * (H / 2) * Wp;
+  long long blocks = (total + 255) / 256;
+  if (blocks > (long long)kSMs * 16) blocks = (long long)kSMs * 16;
+  s2d_stem_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out, N, H, W, C,
+                                                                 H / 2, Wp, lpad);
+  return (int)cudaGetLastError();
+}

@@ -442,7 +442,7 @@ bool plan_persistent(int Ci, int Co, int R, int S, int Ho, int Wo, int* BN_out, 
 
 int launch_halo(const void* in, const void* w, void* out, const float* bias, float* stats, int N, int Hi, int Wi, int Ci,
                 int Ho, int Wo, int Co, int R, int S, int ph, int pw, int b_mn, int flip, int w_rows, long long w_cols_total,
-                int w_cols, cudaStream_t st) {
+                int w_cols, cudaStream_t st, long long xs_w = 0, long long xs_h = 0, long long xs_n = 0) {
   int rc = load_driver_fns();
   if (rc) return rc;
   HaloParams p;
@@ -469,7 +469,7 @@ int launch_halo(const void* in, const void* w, void* out, const float* bias, flo
   if (smem > 200 * 1024) return -3;
   p.D = out; p.ldd = Co; p.bias = bias; p.stats = stats;
   CUtensorMap ta, tb;
-  rc = make_map_nhwc_tiled(&ta, in, N, Hi, Wi, Ci, p.pitch, box_h);
+  rc = make_map_nhwc_tiled(&ta, in, N, Hi, Wi, Ci, p.pitch, box_h, xs_w, xs_h, xs_n);
   if (rc) return rc;
   rc = b_mn ? make_map_2d(&tb, w, w_rows, w_cols_total, w_cols_total, 64, 64)
             : make_map_2d(&tb, w, w_rows, w_cols_total, w_cols_total, 64, p.BN);
@@ -524,6 +524,17 @@ MPB_API int mpb_tc_conv_fprop_halo(const void* x, const void* w, void* y, const 
   if (C % 8 != 0 || K % 8 != 0) return -2;
   return launch_halo(x, w, y, bias, stats, N, H, W, C, P, Q, K, R, S, pad_h, pad_w, /*b_mn=*/0, /*flip=*/0,
                      /*w_rows=*/K, /*w_cols_total=*/(long long)R * S * C, /*w_cols=*/0, (cudaStream_t)stream);
+}
+
+// Same, with explicit element strides of x between pixels / rows / images.  A pixel stride smaller than C describes
+// overlapping super-pixels: the space-to-depth form of the 7x7/2 stem reads 4 neighbouring 16-channel pixels as one
+// 64-channel pixel that advances by 16 elements (mpb_s2d_stem below builds that buffer).
+MPB_API int mpb_tc_conv_fprop_halo_strided(const void* x, const void* w, void* y, const float* bias, float* stats, int N,
+                                           int H, int W, int C, int K, int R, int S, int P, int Q, int pad_h, int pad_w,
+                                           long long xs_w, long long xs_h, long long xs_n, void* stream) {
+  if (C % 8 != 0 || K % 8 != 0) return -2;
+  return launch_halo(x, w, y, bias, stats, N, H, W, C, P, Q, K, R, S, pad_h, pad_w, 0, 0, K, (long long)R * S * C, 0,
+                     (cudaStream_t)stream, xs_w, xs_h, xs_n);
 }
 
 // dx[N,H,W,C] for a stride-1 convolution: a stride-1 convolution of dy with the flipped filter, pad' = R-1-pad.

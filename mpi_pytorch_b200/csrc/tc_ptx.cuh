@@ -196,9 +196,15 @@ static int make_map_im2col(CUtensorMap* m, const void* ptr, int N, int H, int W,
 
 // tiled 4-D map over an NHWC bf16 tensor: dims {C, W, H, N}; box {64 channels, box_w, box_h, 1}; out-of-range
 // coordinates (negative or past the edge) are zero-filled -- this is how a halo tile gets its padding
-static int make_map_nhwc_tiled(CUtensorMap* m, const void* ptr, int N, int H, int W, int C, int box_w, int box_h) {
+static int make_map_nhwc_tiled(CUtensorMap* m, const void* ptr, int N, int H, int W, int C, int box_w, int box_h,
+                               long long w_stride = 0, long long h_stride = 0, long long n_stride = 0) {
+  // strides in elements; 0 = dense NHWC.  A pixel stride SMALLER than C describes overlapping "super-pixels"
+  // (the space-to-depth stem: 64 = 4 neighbouring pixels x 16 channels, advancing one pixel = 16 elements per W index)
+  if (w_stride <= 0) w_stride = C;
+  if (h_stride <= 0) h_stride = (long long)W * w_stride;
+  if (n_stride <= 0) n_stride = (long long)H * h_stride;
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint64_t strides[3] = {(cuuint64_t)w_stride * 2, (cuuint64_t)h_stride * 2, (cuuint64_t)n_stride * 2};
   cuuint32_t box[4] = {(cuuint32_t)BK, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
   cuuint32_t es[4] = {1, 1, 1, 1};
   CUresult r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,

@@ -267,15 +267,16 @@ void wg_grid(const WgParams& p, int N, int* gx, int* ygroups, int* num_tiles) {
 // dw[K,R,S,C] (fp32, zero-initialised or partially accumulated) += wgrad of a stride-1, dilation-1 convolution.
 // Every CTA adds its accumulators into dw with coalesced fp32 RED operations (parking per-CTA partial sums in a
 // workspace and folding them with a second kernel measured 5-20 us SLOWER per layer on B200).
-MPB_API int mpb_tc_conv_wgrad_halo(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R,
-                                   int S, int P, int Q, int pad_h, int pad_w, void* stream) {
+static int wgrad_halo_launch(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R, int S,
+                             int P, int Q, int pad_h, int pad_w, long long xs_w, long long xs_h, long long xs_n,
+                             void* stream) {
   int rc = load_driver_fns();
   if (rc) return rc;
   WgParams p;
   if (!plan_wgrad(C, K, R, S, P, Q, &p)) return -2;
   p.N = N; p.Ho = P; p.Wo = Q; p.C = C; p.K = K; p.R = R; p.S = S; p.ph = pad_h; p.pw = pad_w; p.dw = dw;
   CUtensorMap tx, td;
-  rc = make_map_nhwc_tiled(&tx, x, N, H, W, C, p.pitch, p.TR + (p.pair ? R - 1 : 0));
+  rc = make_map_nhwc_tiled(&tx, x, N, H, W, C, p.pitch, p.TR + (p.pair ? R - 1 : 0), xs_w, xs_h, xs_n);
   if (rc) return rc;
   rc = make_map_nhwc_tiled(&td, dy, N, P, Q, K, p.pitch, p.TR);
   if (rc) return rc - 1000;
@@ -292,4 +293,16 @@ MPB_API int mpb_tc_conv_wgrad_halo(const void* dy, const void* x, float* dw, int
   dim3 grid((unsigned)gx, (unsigned)ygroups, 1);
   tc_wgrad_halo_kernel<<<grid, kThreads, smem, st>>>(tx, td, p, num_tiles);
   return (int)cudaGetLastError();
+}
+
+MPB_API int mpb_tc_conv_wgrad_halo(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K, int R,
+                                   int S, int P, int Q, int pad_h, int pad_w, void* stream) {
+  return wgrad_halo_launch(dy, x, dw, N, H, W, C, K, R, S, P, Q, pad_h, pad_w, 0, 0, 0, stream);
+}
+
+// x given with explicit element strides between pixels / rows / images (see mpb_tc_conv_fprop_halo_strided).
+MPB_API int mpb_tc_conv_wgrad_halo_strided(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int K,
+                                           int R, int S, int P, int Q, int pad_h, int pad_w, long long xs_w,
+                                           long long xs_h, long long xs_n, void* stream) {
+  return wgrad_halo_launch(dy, x, dw, N, H, W, C, K, R, S, P, Q, pad_h, pad_w, xs_w, xs_h, xs_n, stream);
 }

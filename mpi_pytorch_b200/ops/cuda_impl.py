@@ -94,7 +94,10 @@ class _ConvFn(torch.autograd.Function):
         tc = _gemm()
         stats = None
         ctx.xcol = None
-        if tc.fprop_ok(x, w, stride, padding, dilation, groups):
+        ctx.xs2d = None
+        if tc.stem_s2d_ok(x, w, stride, padding, dilation, groups):
+            y, stats, ctx.xs2d = tc.conv_fprop_stem(x, w, None if bias is None else bias.detach(), padding, want_stats)
+        elif tc.fprop_ok(x, w, stride, padding, dilation, groups):
             y, stats = tc.conv_fprop(x, w, None if bias is None else bias.detach(), stride, padding, want_stats)
         elif tc.im2col_ok(x, w, stride, padding, dilation, groups):
             y, stats, ctx.xcol = tc.conv_fprop_im2col(x, w, None if bias is None else bias.detach(), stride, padding,
@@ -122,6 +125,9 @@ class _ConvFn(torch.autograd.Function):
         if need_x and tc.dgrad_ok(*args):
             gx = tc.conv_dgrad(gy, w, x.shape, stride, padding)
             need_x = False
+        if need_w and ctx.xs2d is not None:
+            gw = tc.conv_wgrad_stem(gy, ctx.xs2d, x.shape, w.shape, padding).to(wdtype)
+            need_w = False
         if need_w and ctx.xcol is not None:
             gw = tc.conv_wgrad_im2col(gy, ctx.xcol, w.shape).to(wdtype)
             need_w = False

@@ -265,3 +265,84 @@ def conv_wgrad_im2col(gy, xcol, w_shape) -> torch.Tensor:
     splitk = max(1, min(8 * SMS // max(1, (kp + 127) // 128), (m + 63) // 64 // 96))
     dw = gemm(gy2d, xcol, k, kp, m, True, True, out_dtype=torch.float32, splitk=max(2, splitk))
     return dw[:, : c * r * s].reshape(k, r, s, c).permute(0, 3, 1, 2)            # logical (K,C,R,S)
+
+
+# ------------------------------------------------------------------------------------------- space-to-depth stems
+STEM_S2D = os.environ.get("MPB_TC_STEM_S2D", "1") != "0"
+_S2D_IDX = {}
+
+
+def stem_s2d_ok(x, w, stride, padding, dilation, groups) -> bool:
+    """7x7 stride-2 convolutions over <= 4 input channels (ResNet / DenseNet / SqueezeNet stems) run as a 4x1 stride-1
+    convolution with 64 'channels' over a space-to-depth copy of the input (no im2col matrix); models.py:33,68,81."""
+    if not STEM_S2D or x.dtype != torch.bfloat16 or groups != 1 or tuple(dilation) != (1, 1) or tuple(stride) != (2, 2):
+        return False
+    k, c, r, s = w.shape
+    return (r == 7 and s == 7 and 4 * c <= 16 and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0 and k % 64 == 0
+            and padding[0] == padding[1] and 0 <= padding[0] <= 3)
+
+
+def _s2d_index(c: int, pad: int, device):
+    """Gather maps between the KRSC filter (7*7*c per output channel, + one zero slot) and its s2d form [4][64]."""
+    key = (c, pad, str(device))
+    if key not in _S2D_IDX:
+        off, zero = pad % 2, 49 * c
+        fwd = torch.full((4 * 64,), zero, dtype=torch.int64)
+        inv = torch.zeros(49 * c, dtype=torch.int64)
+        for a in range(4):
+            for a2 in range(4):
+                for b in range(2):
+                    for b2 in range(2):
+                        r, s = 2 * a + b - off, 2 * a2 + b2 - off
+                        if 0 <= r < 7 and 0 <= s < 7:
+                            for ch in range(c):
+                                dst = a * 64 + a2 * 16 + (b * 2 + b2) * c + ch
+                                fwd[dst] = (r * 7 + s) * c + ch
+                                inv[(r * 7 + s) * c + ch] = dst
+        _S2D_IDX[key] = (fwd.to(device), inv.to(device))
+    return _S2D_IDX[key]
+
+
+def _s2d_geom(x_shape, w_shape, padding):
+    n, c, h, wd = x_shape
+    k = w_shape[0]
+    pad = padding[0]
+    p, q = (h + 2 * pad - 7) // 2 + 1, (wd + 2 * pad - 7) // 2 + 1
+    lpad = (pad + 1) // 2                              # rows / pixels of zero padding in s2d space (top / left)
+    wp = max(q + 3, lpad + wd // 2)
+    return n, c, h, wd, k, p, q, lpad, wp
+
+
+def conv_fprop_stem(x, w, bias, padding, want_stats=False):
+    """-> (y, stats, xs2d).  xs2d ([N, H/2, Wp, 16] bf16) is kept for the wgrad."""
+    n, c, h, wd, k, p, q, lpad, wp = _s2d_geom(x.shape, w.shape, padding)
+    xs = torch.empty((n, h // 2, wp, 16), dtype=torch.bfloat16, device=x.device)
+    rc = _LIB.mpb_s2d_stem(_p(x), _p(xs), c_int(n), c_int(h), c_int(wd), c_int(c), c_int(wp), c_int(lpad),
+                           c_void_p(_stream()))
+    _check(rc, "mpb_s2d_stem")
+    fwd, _ = _s2d_index(c, padding[0], x.device)
+    wk = w.permute(0, 2, 3, 1).reshape(k, 49 * c)
+    w2 = torch.cat([wk, wk.new_zeros(k, 1)], dim=1)[:, fwd].contiguous()             # [K][4 taps][64]
+    y = torch.empty((n, k, p, q), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
+    stats = _scratch.take(2 * k, x.device)[0] if want_stats else None
+    ll = ctypes.c_longlong
+    rc = _LIB.mpb_tc_conv_fprop_halo_strided(_p(xs), _p(w2), _p(y), _p(None if bias is None else bias.float()), _p(stats),
+                                             c_int(n), c_int(h // 2), c_int(wp - 3), c_int(64), c_int(k), c_int(4),
+                                             c_int(1), c_int(p), c_int(q), c_int(lpad), c_int(0), ll(16), ll(wp * 16),
+                                             ll((h // 2) * wp * 16), c_void_p(_stream()))
+    LAUNCHES["n"] += 2 + int(want_stats)
+    _check(rc, "mpb_tc_conv_fprop_halo_strided")
+    return y, stats, xs
+
+
+def conv_wgrad_stem(gy, xs, x_shape, w_shape, padding) -> torch.Tensor:
+    n, c, h, wd, k, p, q, lpad, wp = _s2d_geom(x_shape, w_shape, padding)
+    dw2 = torch.zeros((k, 4 * 64), dtype=torch.float32, device=gy.device)
+    ll = ctypes.c_longlong
+    rc = _LIB.mpb_tc_conv_wgrad_halo_strided(_p(gy), _p(xs), _p(dw2), c_int(n), c_int(h // 2), c_int(wp - 3), c_int(64),
+                                             c_int(k), c_int(4), c_int(1), c_int(p), c_int(q), c_int(lpad), c_int(0),
+                                             ll(16), ll(wp * 16), ll((h // 2) * wp * 16), c_void_p(_stream()))
+    LAUNCHES["n"] += 1
+    _check(rc, "mpb_tc_conv_wgrad_halo_strided")
+    _, inv = _s2d_index(c, padding[0], gy.device)
+    return dw2[:, inv].reshape(k, 7, 7, c).permute(0, 3, 1, 2)                      # logical (K,C,R,S)

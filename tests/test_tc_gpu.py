@@ -51,6 +51,26 @@ CONVS = [(2, 64, 8, 8, 64, 1, 1, 0), (2, 64, 8, 8, 64, 3, 1, 1), (8, 64, 56, 56,
          (37, 64, 28, 28, 64, 3, 1, 1)]
 
 
+@pytest.mark.parametrize("n,hw,k,pad", [(4, 64, 64, 3), (3, 38, 128, 2), (2, 30, 64, 0), (5, 32, 64, 1)])
+def test_stem_space_to_depth_conv(n, hw, k, pad):
+    """7x7/2 stems over 3 channels as a 4x1 convolution over overlapping space-to-depth super-pixels."""
+    tc = _tc()
+    torch.manual_seed(3)
+    x = torch.randn(n, 3, hw, hw + 2, device="cuda").bfloat16().contiguous(memory_format=torch.channels_last)
+    wt = (torch.randn(k, 3, 7, 7, device="cuda") * 0.1).bfloat16().contiguous(memory_format=torch.channels_last)
+    assert tc.stem_s2d_ok(x, wt, (2, 2), (pad, pad), (1, 1), 1)
+    xf, wf = x.float(), wt.float().requires_grad_(True)
+    yref = F.conv2d(xf, wf, None, 2, pad)
+    gy = torch.randn_like(yref).bfloat16().contiguous(memory_format=torch.channels_last)
+    yref.backward(gy.float())
+    y, stats, xs = tc.conv_fprop_stem(x, wt, None, (pad, pad), True)
+    assert y.shape == yref.shape and _rel(y, yref) < 8e-3
+    assert _rel(stats[:k], yref.sum(dim=(0, 2, 3))) < 1e-4
+    assert _rel(stats[k:], (yref * yref).sum(dim=(0, 2, 3))) < 1e-4
+    dw = tc.conv_wgrad_stem(gy, xs, x.shape, wt.shape, (pad, pad))
+    assert dw.shape == wf.grad.shape and _rel(dw, wf.grad) < 2e-4
+
+
 def test_wgrad_halo_kernel_covers_the_resnet_layers():
     tc = _tc()
     for (c, k, hw) in ((64, 64, 56), (128, 128, 28), (256, 256, 14)):
