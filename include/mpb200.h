@@ -115,7 +115,7 @@ int mpb_tc_conv_dgrad(const void* dy, const void* w, void* dx, int N, int H, int
 /* Halo-tile variants for stride-1 filters larger than 1x1: the activation tile (with halo) is fetched once per
  * 64-channel block and every filter tap is a row-shifted UMMA view of it.  mpb_tc_halo_efficiency = fraction of the
  * 128 GEMM rows that are real output pixels for a geometry.                                                     */
-float mpb_tc_halo_efficiency(int Ho, int Wo, int S);
+float mpb_tc_halo_efficiency(int Ho, int Wo, int R, int S);
 int mpb_tc_halo_persistent_ok(int Ci, int Co, int R, int S, int Ho, int Wo);
 int mpb_tc_conv_fprop_halo(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H, int W,
                            int C, int K, int R, int S, int P, int Q, int pad_h, int pad_w, void* stream);

@@ -402,18 +402,28 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   }
 }
 
-// Tile geometry: whole padded rows when they fit in 128 GEMM rows, otherwise one row split into column tiles.
-void pick_tile(int Ho, int Wo, int S, int* TR, int* TW) {
-  if (Wo + S - 1 <= 128) {
-    *TW = Wo;
-    int tr = 128 / (Wo + S - 1);
-    *TR = tr < Ho ? tr : Ho;
-  } else {
-    const int maxw = 128 - (S - 1);
-    const int parts = (Wo + maxw - 1) / maxw;
-    *TW = (Wo + parts - 1) / parts;
-    *TR = 1;
+// Tile geometry: TR rows x TW columns of output with TR * (TW + S - 1) <= 128 GEMM rows.  Among the splits of a row
+// into 1..8 column parts pick the one that fills the 128 rows best, discounted by how much halo the tile drags in
+// ((TR + R - 1) * pitch pixels loaded per TR * TW outputs): narrow-and-tall tiles re-read fewer halo rows.
+void pick_tile(int Ho, int Wo, int R, int S, int* TR, int* TW) {
+  const int forced = env_int("MPB_HALO_PARTS", 0);
+  double best = -1.0;
+  for (int parts = 1; parts <= 8; ++parts) {
+    if (forced && parts != forced) continue;
+    const int tw = (Wo + parts - 1) / parts;
+    const int pitch = tw + S - 1;
+    if (pitch > 128) continue;
+    int tr = 128 / pitch;
+    if (tr > Ho) tr = Ho;
+    if (tr < 1) continue;
+    const int tiles = ((Ho + tr - 1) / tr) * ((Wo + tw - 1) / tw);
+    const double eff = (double)Ho * Wo / ((double)tiles * 128.0);
+    const double halo = (double)(tr + R - 1) * pitch / ((double)tr * tw);
+    const double score = eff / (1.0 + 0.15 * (halo - 1.0));
+    if (score > best * 1.0001) { best = score; *TR = tr; *TW = tw; }
+    if (tw == 1) break;
   }
+  if (best < 0) { *TW = 128 - (S - 1); *TR = 1; }
 }
 
 // Can the persistent, weights-resident variant run this layer, and with which tile width?  Prefers BN = 128 and
@@ -421,7 +431,7 @@ void pick_tile(int Ho, int Wo, int S, int* TR, int* TW) {
 // which is still far less traffic than streaming weights per tap).
 bool plan_persistent(int Ci, int Co, int R, int S, int Ho, int Wo, int* BN_out, int* a_stages_out) {
   int TR, TW;
-  pick_tile(Ho, Wo, S, &TR, &TW);
+  pick_tile(Ho, Wo, R, S, &TR, &TW);
   const int pitch = TW + S - 1, box_h = TR + R - 1;
   if (pitch > 256 || box_h > 256) return false;
   const int cblocks = (Ci + BK - 1) / BK;
@@ -448,7 +458,7 @@ int launch_halo(const void* in, const void* w, void* out, const float* bias, flo
   HaloParams p;
   memset(&p, 0, sizeof(p));
   p.N = N; p.Ho = Ho; p.Wo = Wo; p.Co = Co; p.Ci = Ci; p.R = R; p.S = S; p.ph = ph; p.pw = pw;
-  pick_tile(Ho, Wo, S, &p.TR, &p.TW);
+  pick_tile(Ho, Wo, R, S, &p.TR, &p.TW);
   p.pitch = p.TW + S - 1;
   p.tiles_h = (Ho + p.TR - 1) / p.TR; p.tiles_w = (Wo + p.TW - 1) / p.TW;
   p.BN = (Co > 64) ? 128 : 64; p.b_mn = b_mn; p.flip = flip; p.w_cols = w_cols;
@@ -511,9 +521,9 @@ MPB_API int mpb_tc_halo_persistent_ok(int Ci, int Co, int R, int S, int Ho, int 
 }
 
 // Fraction of the 128 GEMM rows that are real output pixels for this geometry (the caller's go / no-go signal).
-MPB_API float mpb_tc_halo_efficiency(int Ho, int Wo, int S) {
+MPB_API float mpb_tc_halo_efficiency(int Ho, int Wo, int R, int S) {
   int TR, TW;
-  pick_tile(Ho, Wo, S, &TR, &TW);
+  pick_tile(Ho, Wo, R, S, &TR, &TW);
   const int th = (Ho + TR - 1) / TR, tw = (Wo + TW - 1) / TW;
   return (float)((double)Ho * Wo / ((double)th * tw * 128.0));
 }

@@ -125,7 +125,7 @@ def halo_ok(out_h: int, out_w: int, r: int, s: int, stride, ci: int = 0, co: int
     halo-tile kernel (activation tile fetched once per channel block instead of once per tap)."""
     if not HALO or stride[0] != 1 or stride[1] != 1 or r * s == 1:
         return False
-    if float(_LIB.mpb_tc_halo_efficiency(c_int(out_h), c_int(out_w), c_int(s))) < HALO_MIN_EFF:
+    if float(_LIB.mpb_tc_halo_efficiency(c_int(out_h), c_int(out_w), c_int(r), c_int(s))) < HALO_MIN_EFF:
         return False
     if HALO_STREAMING:
         return True
