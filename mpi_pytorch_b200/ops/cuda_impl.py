@@ -154,7 +154,11 @@ class _ConvFn(torch.autograd.Function):
             if need_w:
                 gw = fw.to(wdtype)
         if has_bias and ctx.needs_input_grad[2]:
-            gb = gy.float().sum(dim=(0, 2, 3))
+            k = gy.shape[1]
+            if k % 8 == 0 and k <= 2048 and gy.dtype in (torch.bfloat16, torch.float32):
+                gb = bn_stats(gy)[:k]             # one pass over dy in its own dtype (no fp32 copy + library reduction)
+            else:
+                gb = gy.float().sum(dim=(0, 2, 3))
         return gx, gw, gb, None, None, None, None, None
 
 

@@ -17,10 +17,11 @@ def main():
     model = sys.argv[1] if len(sys.argv) > 1 else "resnet34"
     steps = 3
     w = bootstrap.init_world("cuda")
-    s = Settings(MODEL_NAME=model, NUM_CLASSES=1000, BATCH_SIZE=256, HEIGHT=224, WIDTH=224, USE_PRETRAINED=False,
+    bs, hw = int(os.environ.get("MPB_PROF_BATCH", "256")), int(os.environ.get("MPB_PROF_IMAGE", "224"))
+    s = Settings(MODEL_NAME=model, NUM_CLASSES=1000, BATCH_SIZE=bs, HEIGHT=hw, WIDTH=hw, USE_PRETRAINED=False,
                  DTYPE="bf16", LR=4e-4)
     tr = Trainer(s, w)
-    batches = list(iter(tr.make_shard(total=512, shuffle=False)))
+    batches = list(iter(tr.make_shard(total=2 * bs, shuffle=False)))
     for i in range(3):
         tr.train_step(*batches[i % 2])
     torch.cuda.synchronize()

@@ -88,6 +88,25 @@ def _bn_case(dtype, tol, C, relu, res, N, H, W):
     assert int(bn.num_batches_tracked) == 1
 
 
+def test_conv_bias_gradient_single_pass():
+    """dL/db of a biased convolution (VGG / AlexNet / SqueezeNet) comes from one column-sum pass over dy."""
+    torch.manual_seed(4)
+    conv = nn.Conv2d(64, 128, 3, padding=1).cuda()
+    x = cl(torch.randn(4, 64, 12, 12, device="cuda").bfloat16()).requires_grad_(True)
+    y = nat().conv2d(x, conv.weight, conv.bias, (1, 1), (1, 1))
+    g = cl(torch.randn_like(y))
+    y.backward(g)
+    xr = x.detach().float().requires_grad_(True)
+    ref = copy.deepcopy(conv)
+    ref.weight.grad = ref.bias.grad = None
+    with torch.no_grad():
+        ref.weight.copy_(conv.weight.bfloat16().float())
+    F.conv2d(xr, ref.weight, ref.bias, 1, 1).backward(g.float())
+    assert torch.allclose(conv.bias.grad, ref.bias.grad, atol=1e-3, rtol=1e-4)
+    assert torch.allclose(conv.weight.grad, ref.weight.grad, atol=2e-2, rtol=2e-2)
+    assert torch.allclose(x.grad.float(), xr.grad, atol=5e-2, rtol=5e-2)
+
+
 def test_batchnorm_eval():
     C = 64
     x = cl(torch.randn(4, C, 7, 7, device="cuda"))
