@@ -81,6 +81,10 @@ int mpb_adaptive_avgpool(const void* in, void* out, int N, int H, int W, int C, 
 int mpb_relu_fwd(const void* x, void* y, long long n, int dtype, void* stream);
 int mpb_relu_bwd(const void* dy, const void* y, void* dx, long long n, int dtype, void* stream);
 int mpb_dropout(const void* x, void* y, long long n, unsigned int seed, float p, int dtype, void* stream);
+/* M rows of row_bytes (multiple of 16) between row-pitched buffers: channel concat into an NHWC slice and its inverse
+ * (torch.cat of the DenseNet / Inception / Fire blocks, models.py:56-87).                                       */
+int mpb_copy_rows(const void* src, long long src_pitch, void* dst, long long dst_pitch, long long M, long long row_bytes,
+                  void* stream);
 /* `epoch` (nullable device pointer): a step counter mixed into the seed on the device, so a captured launch draws a
  * new mask on every CUDA-graph replay; the backward call of the same step passes the same pointer and seed.      */
 int mpb_dropout_ex(const void* x, void* y, long long n, unsigned int seed, const long long* epoch, float p, int dtype,

@@ -497,3 +497,36 @@ MPB_API int mpb_dropout_ex(const void* x, void* y, long long n, unsigned int see
 MPB_API int mpb_dropout(const void* x, void* y, long long n, unsigned int seed, float p, int dtype, void* stream) {
   return mpb_dropout_ex(x, y, n, seed, nullptr, p, dtype, stream);
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// Row-strided copy: M rows of `row_bytes` (a multiple of 16) from a source with row pitch src_pitch bytes to a
+// destination with row pitch dst_pitch bytes.  This is channel concatenation (write a tensor into its channel slice
+// of the NHWC output) and its inverse (gather a channel slice of a gradient into a dense NHWC tensor) at 16 bytes
+// per thread -- the library's generic strided-copy kernels that torch.cat / .contiguous() use for these views run
+// at a quarter of the copy rate.  (torch.cat at models.py DenseNet / Inception / Fire blocks.)
+// ------------------------------------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) copy_rows_kernel(const uint8_t* __restrict__ src, long long src_pitch,
+                                                        uint8_t* __restrict__ dst, long long dst_pitch, long long M,
+                                                        int vecs_per_row) {
+  const long long total = M * vecs_per_row;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / vecs_per_row;
+    const int v = (int)(i - row * vecs_per_row);
+    const uint4 u = *reinterpret_cast<const uint4*>(src + row * src_pitch + (long long)v * 16);
+    *reinterpret_cast<uint4*>(dst + row * dst_pitch + (long long)v * 16) = u;
+  }
+}
+}  // namespace
+
+MPB_API int mpb_copy_rows(const void* src, long long src_pitch, void* dst, long long dst_pitch, long long M,
+                          long long row_bytes, void* stream) {
+  if (row_bytes % 16 != 0 || src_pitch % 16 != 0 || dst_pitch % 16 != 0 || ((uintptr_t)src & 15) || ((uintptr_t)dst & 15))
+    return -1;
+  if (M <= 0 || row_bytes == 0) return 0;
+  const int vecs = (int)(row_bytes / 16);
+  copy_rows_kernel<<<grid_for(M * vecs, 256, 16), 256, 0, (cudaStream_t)stream>>>((const uint8_t*)src, src_pitch, (uint8_t*)dst,
+                                                                                  dst_pitch, M, vecs);
+  MPB_CHECK_LAUNCH();
+  return 0;
+}

@@ -136,4 +136,6 @@ def normalize_u8(img_u8_nhwc, dtype=torch.float32):
 
 def cat_channels(tensors):
     """Channel concat (DenseNet / Inception / Fire)."""
+    if _nat(tensors[0]):
+        return native().cat_channels(tensors)
     return torch.cat(tensors, dim=1)

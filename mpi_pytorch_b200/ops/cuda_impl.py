@@ -60,8 +60,31 @@ def _note_fallback(op: str) -> None:
     FALLBACKS[op] = FALLBACKS.get(op, 0) + 1
 
 
+def _row_view(t: torch.Tensor):
+    """(rows, channels, channel pitch) if ``t`` (NCHW-shaped) is stored as NHWC rows with a channel pitch >= C -- i.e.
+    a channel slice of a wider channels-last tensor (what the backward of a channel concat hands out)."""
+    if t.dim() != 4:
+        return None
+    n, c, h, w = t.shape
+    sn, sc, sh, sw = t.stride()
+    if (c > 1 and sc != 1) or sw < c or (h > 1 and sh != w * sw) or (n > 1 and sn != h * w * sw):
+        return None
+    return n * h * w, c, sw
+
+
+def _copy_rows(src_ptr: int, src_pitch: int, dst_ptr: int, dst_pitch: int, rows: int, row_bytes: int) -> None:
+    _call("mpb_copy_rows", c_void_p(src_ptr), c_ll(src_pitch), c_void_p(dst_ptr), c_ll(dst_pitch), c_ll(rows),
+          c_ll(row_bytes), c_void_p(_stream()))
+
+
 def _nhwc(x: torch.Tensor) -> torch.Tensor:
     if x.dim() == 4 and not x.is_contiguous(memory_format=torch.channels_last):
+        rv = _row_view(x) if x.is_cuda else None
+        eb = x.element_size()
+        if rv is not None and (rv[1] * eb) % 16 == 0 and (rv[2] * eb) % 16 == 0 and x.data_ptr() % 16 == 0:
+            out = torch.empty(x.shape, dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+            _copy_rows(x.data_ptr(), rv[2] * eb, out.data_ptr(), rv[1] * eb, rv[0], rv[1] * eb)     # 16 B per thread
+            return out
         return x.contiguous(memory_format=torch.channels_last)
     return x
 
@@ -323,6 +346,43 @@ def _bn_ok_channels(c: int) -> bool:
     return c % 8 == 0 and c <= 2048
 
 
+# =============================================================================== channel concat
+class _CatFn(torch.autograd.Function):
+    """Channel concat of NHWC tensors: each input is written into its channel slice with the row-strided copy kernel;
+    backward hands out channel-slice views of the gradient (consumers gather them with the same kernel)."""
+
+    @staticmethod
+    def forward(ctx, *tensors):
+        ts = [_nhwc(t) for t in tensors]
+        n, _, h, w = ts[0].shape
+        cs = [int(t.shape[1]) for t in ts]
+        ct, eb = sum(cs), ts[0].element_size()
+        out = torch.empty((n, ct, h, w), dtype=ts[0].dtype, device=ts[0].device, memory_format=torch.channels_last)
+        off = 0
+        for t, c in zip(ts, cs):
+            _copy_rows(t.data_ptr(), c * eb, out.data_ptr() + off * eb, ct * eb, n * h * w, c * eb)
+            off += c
+        ctx.cs = cs
+        return out
+
+    @staticmethod
+    def backward(ctx, gy):
+        outs, off = [], 0
+        for c in ctx.cs:
+            outs.append(gy[:, off:off + c])
+            off += c
+        return tuple(outs)
+
+
+def cat_channels(tensors):
+    t0 = tensors[0]
+    ok = all(t.dim() == 4 and t.is_cuda and t.dtype == t0.dtype and t.shape[0] == t0.shape[0] and t.shape[2:] == t0.shape[2:]
+             and (t.shape[1] * t.element_size()) % 16 == 0 for t in tensors)
+    if not ok or t0.dtype not in (torch.bfloat16, torch.float32, torch.float16):
+        return torch.cat(list(tensors), dim=1)
+    return _CatFn.apply(*tensors)
+
+
 # =============================================================================== elementwise
 class _ReluFn(torch.autograd.Function):
     @staticmethod
@@ -335,8 +395,7 @@ class _ReluFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, gy):
         (y,) = ctx.saved_tensors
-        gy = gy.contiguous(memory_format=torch.channels_last) if (y.dim() == 4 and y.is_contiguous(
-            memory_format=torch.channels_last)) else gy.contiguous()
+        gy = _nhwc(gy) if (y.dim() == 4 and y.is_contiguous(memory_format=torch.channels_last)) else gy.contiguous()
         dx = torch.empty_like(y)
         _call("mpb_relu_bwd", _p(gy), _p(y), _p(dx), c_ll(y.numel()), c_int(_dt(y)), c_void_p(_stream()))
         return dx

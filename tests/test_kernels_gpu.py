@@ -107,6 +107,33 @@ def test_conv_bias_gradient_single_pass():
     assert torch.allclose(x.grad.float(), xr.grad, atol=5e-2, rtol=5e-2)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_channel_concat_and_slice_gather(dtype):
+    """cat_channels writes each input into its NHWC channel slice; its backward hands out slice views that the
+    consumers gather with the same row-strided copy kernel."""
+    torch.manual_seed(6)
+    n = nat()
+    xs = [cl(torch.randn(3, c, 9, 7, device="cuda").to(dtype)).requires_grad_(True) for c in (64, 8, 96)]
+    y = n.cat_channels(xs)
+    assert y.is_contiguous(memory_format=torch.channels_last)
+    assert torch.equal(y, torch.cat([x.detach() for x in xs], 1))
+    z = n.relu(y)                                   # a consumer whose backward receives the full gradient
+    g = cl(torch.randn_like(z))
+    z.backward(g)
+    off = 0
+    for x in xs:
+        c = x.shape[1]
+        want = (g * (y > 0))[:, off:off + c]
+        assert torch.equal(x.grad, want)
+        off += c
+    # a channel-slice view gathers into a dense NHWC tensor without the library's generic strided copy
+    big = cl(torch.randn(2, 160, 5, 6, device="cuda").to(dtype))
+    sl = big[:, 32:96]
+    from mpi_pytorch_b200.ops import cuda_impl
+    dense = cuda_impl._nhwc(sl)
+    assert dense.is_contiguous(memory_format=torch.channels_last) and torch.equal(dense, sl)
+
+
 def test_batchnorm_eval():
     C = 64
     x = cl(torch.randn(4, C, 7, 7, device="cuda"))
