@@ -349,7 +349,8 @@ def _bn_ok_channels(c: int) -> bool:
 # =============================================================================== channel concat
 class _CatFn(torch.autograd.Function):
     """Channel concat of NHWC tensors: each input is written into its channel slice with the row-strided copy kernel;
-    backward hands out channel-slice views of the gradient (consumers gather them with the same kernel)."""
+    backward gathers each input's channel slice of the gradient into a dense tensor with the same kernel, so whatever
+    consumes it next -- one of our kernels or autograd's own accumulation (DenseNet: O(L^2) adds) -- runs vectorised."""
 
     @staticmethod
     def forward(ctx, *tensors):
@@ -368,8 +369,8 @@ class _CatFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, gy):
         outs, off = [], 0
-        for c in ctx.cs:
-            outs.append(gy[:, off:off + c])
+        for i, c in enumerate(ctx.cs):
+            outs.append(_nhwc(gy[:, off:off + c]) if ctx.needs_input_grad[i] else None)
             off += c
         return tuple(outs)
 
