@@ -22,6 +22,7 @@ using namespace mpbtc;
 namespace {
 
 constexpr int kThreads = 192;
+constexpr int kThreadsPersist = 320;      // persistent kernel: 8 epilogue warps, two per TMEM lane quarter (each takes half the columns)
 
 __device__ __forceinline__ void tma_load_4d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1, int c2, int c3) {
   asm volatile(
@@ -216,7 +217,7 @@ tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // Per tile the tensor core issues R*S*cblocks*4 MMAs while TMA brings one halo tile per channel block: the loop is
 // MMA-bound instead of L2-fabric-bound.
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreadsPersist, 1)
 tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const HaloParams p,
                        int num_tiles) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -238,7 +239,7 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     prefetch_tmap(&tmB);
     for (int i = 0; i < p.a_stages; ++i) { mbar_init(&full_a[i], 1); mbar_init(&empty_a[i], 1); }
     mbar_init(&full_w, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }   // 4 epilogue warps
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 8); }   // 8 epilogue warps
     fence_barrier_init();
   }
   if (p.stats) for (int j = threadIdx.x; j < 256; j += blockDim.x) { stat_smem[0][j] = 0.f; stat_smem[1][j] = 0.f; }
@@ -318,6 +319,9 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   } else {
     // ================================ epilogue ================================
     const int quarter = warp & 3;
+    // the epilogue is the longer side of the tile pipeline on 64-channel layers (elimination experiments):
+    // two warps share each lane quarter and split the columns
+    const int c_lo = ((warp - 2) >> 2) * (p.BN / 2), c_hi = c_lo + p.BN / 2;
     const int m = quarter * 32 + lane;
     const int tr = m / p.pitch, j = m % p.pitch;
     int it = 0;
@@ -332,13 +336,13 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const long long pix = ((long long)img * p.Ho + p0 + tr) * p.Wo + j0 + j;
       mbar_wait(&tmem_full[acc], (it >> 1) & 1);
       tc_fence_after();
-      for (int c = 0; c < p.BN; c += 32) {
+      for (int c = c_lo; c < c_hi; c += 32) {
         uint32_t rr[32];
         tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)acc * acc_cols + (uint32_t)c, rr);
         float v[32];
 #pragma unroll
         for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(rr[q]);
-        if (c + 32 >= p.BN) {                      // last chunk read: hand the accumulator back to the MMA warp early
+        if (c + 32 >= c_hi) {                      // last chunk read: hand the accumulator back to the MMA warp early
           tc_fence_before();
           __syncwarp();
           if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&tmem_empty[acc])) : "memory");
@@ -503,7 +507,7 @@ int launch_halo(const void* in, const void* w, void* out, const float* bias, flo
     if (ctas < 1) ctas = 1;
     if (ctas > num_tiles) ctas = num_tiles;
     dim3 gridp((unsigned)ctas, (unsigned)n_tiles_y, 1);
-    tc_halo_persist_kernel<<<gridp, kThreads, smem_p, st>>>(ta, tb, p, num_tiles);
+    tc_halo_persist_kernel<<<gridp, kThreadsPersist, smem_p, st>>>(ta, tb, p, num_tiles);
     return (int)cudaGetLastError();
   }
   dim3 grid((unsigned)(N * p.tiles_h * p.tiles_w), (unsigned)((Co + p.BN - 1) / p.BN), 1);
