@@ -224,7 +224,7 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int cblocks = (p.Ci + BK - 1) / BK, taps = p.R * p.S;
   uint8_t* smem_w = smem + (size_t)p.a_stages * p.a_stage_bytes;       // resident weights: [cb][tap] tiles of b_stage_bytes
-  __shared__ uint64_t full_a[8], empty_a[8], full_w, tmem_full[2], tmem_empty[2];
+  __shared__ uint64_t full_a[8], empty_a[8], full_w, tmem_full[4], tmem_empty[4];
   __shared__ uint32_t tmem_base_smem;
   __shared__ float stat_smem[2][256];
 
@@ -232,14 +232,16 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   const int n0 = blockIdx.y * p.BN;
   uint32_t acc_cols = 32;
   while ((int)acc_cols < p.BN) acc_cols <<= 1;
-  const uint32_t tmem_cols = acc_cols * 2;                              // two accumulators
+  // accumulator ring in TMEM: 4 deep when it fits in the 512 columns (the MMA warp then never waits for the epilogue)
+  const int n_acc = (acc_cols * 4 <= 512) ? 4 : 2;
+  const uint32_t tmem_cols = acc_cols * (uint32_t)n_acc;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     for (int i = 0; i < p.a_stages; ++i) { mbar_init(&full_a[i], 1); mbar_init(&empty_a[i], 1); }
     mbar_init(&full_w, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 8); }   // 8 epilogue warps
+    for (int i = 0; i < 4; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 8); }   // 8 epilogue warps
     fence_barrier_init();
   }
   if (p.stats) for (int j = threadIdx.x; j < 256; j += blockDim.x) { stat_smem[0][j] = 0.f; stat_smem[1][j] = 0.f; }
@@ -284,8 +286,8 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     mbar_wait(&full_w, 0);
     int ia = 0, it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int acc = it & 1;
-      mbar_wait(&tmem_empty[acc], ((it >> 1) & 1) ^ 1);      // the epilogue drained this accumulator
+      const int acc = it % n_acc;
+      mbar_wait(&tmem_empty[acc], ((it / n_acc) & 1) ^ 1);   // the epilogue drained this accumulator
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)acc * acc_cols;
       for (int cb = 0; cb < cblocks; ++cb, ++ia) {
@@ -326,7 +328,7 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     const int tr = m / p.pitch, j = m % p.pitch;
     int it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-      const int acc = it & 1;
+      const int acc = it % n_acc;
       int t = tile;
       const int tw = t % p.tiles_w; t /= p.tiles_w;
       const int th = t % p.tiles_h;
@@ -334,7 +336,7 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       const int p0 = th * p.TR, j0 = tw * p.TW;
       const bool row_ok = tr < p.TR && j < p.TW && (p0 + tr) < p.Ho && (j0 + j) < p.Wo;
       const long long pix = ((long long)img * p.Ho + p0 + tr) * p.Wo + j0 + j;
-      mbar_wait(&tmem_full[acc], (it >> 1) & 1);
+      mbar_wait(&tmem_full[acc], (it / n_acc) & 1);
       tc_fence_after();
       for (int c = c_lo; c < c_hi; c += 32) {
         uint32_t rr[32];
