@@ -178,6 +178,9 @@ int mpb_mc_create(long long bytes, int num_devices, int* fd_out, unsigned long l
 int mpb_mc_import(int fd, unsigned long long* mc_out);
 int mpb_mc_add_device(unsigned long long mc);
 int mpb_mc_bind_map(unsigned long long mc, unsigned long long mem_handle, long long bytes, void** mc_ptr);
+/* in-place average of W symmetric bf16 buffers (n % (8*W) == 0): fp32 accumulation in rank order, one rounding */
+int mpb_allreduce_bf16(void* const* bufs, void* const* pads, void* epochs, long long n, int rank, int W, int blocks,
+                       void* stream);
 int mpb_broadcast(void* const* bufs, void* const* pads, void* epochs, long long n_floats, int rank, int W, int root,
                   int blocks, void* stream);
 int mpb_allgather_slices(void* const* bufs, void* const* pads, void* epochs, long long n_floats, int rank, int W,

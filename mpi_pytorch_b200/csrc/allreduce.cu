@@ -316,6 +316,60 @@ __global__ void count_allreduce_kernel(CountParams P) {
   if (threadIdx.x == 0) { *P.out = s; P.epochs[0] = e0 + 2; }
 }
 
+// bf16 buffers (gradients kept in bf16 by the caller: half the NVLink bytes of the fp32 path): two-shot average with
+// fp32 accumulation in rank order, result rounded once and pushed to every peer.
+struct Bf16Params { PeerBufs bufs; PeerBufs pads; uint32_t* epochs; long long n8; int rank, W; float scale; };
+
+__device__ __forceinline__ uint4 ld_peer_u4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_u4(void* p, const uint4& v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <int W>
+__global__ void __launch_bounds__(MPB_COMM_THREADS, 1) allreduce_bf16_kernel(Bf16Params P) {
+  const uint32_t e0 = P.epochs[blockIdx.x];
+  rank_barrier(P.pads, P.rank, W, e0 + 1);
+  constexpr int U = (W <= 2) ? 8 : (W <= 4 ? 4 : 2);          // U * W 16-byte peer loads in flight per thread
+  const long long slice8 = P.n8 / W, base = slice8 * P.rank;
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x, nthreads = (long long)gridDim.x * blockDim.x;
+  for (long long j0 = 0; j0 < slice8; j0 += nthreads * U) {
+    uint4 u[U][W];
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const long long j = j0 + (long long)k * nthreads + tid;
+      if (j < slice8) {
+#pragma unroll
+        for (int p = 0; p < W; ++p) u[k][p] = ld_peer_u4(reinterpret_cast<const uint4*>(P.bufs.p[p]) + base + j);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const long long j = j0 + (long long)k * nthreads + tid;
+      if (j >= slice8) continue;
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int p = 0; p < W; ++p) {                            // rank order: identical bits on every rank
+        const unsigned w[4] = {u[k][p].x, u[k][p].y, u[k][p].z, u[k][p].w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { acc[2 * i] += __uint_as_float(w[i] << 16); acc[2 * i + 1] += __uint_as_float(w[i] & 0xFFFF0000u); }
+      }
+      uint4 r;
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(acc[2 * i] * P.scale, acc[2 * i + 1] * P.scale);
+#pragma unroll
+      for (int p = 0; p < W; ++p) st_peer_u4(reinterpret_cast<uint4*>(P.bufs.p[p]) + base + j, r);
+    }
+  }
+  rank_barrier(P.pads, P.rank, W, e0 + 2);
+  if (threadIdx.x == 0) P.epochs[blockIdx.x] = e0 + 2;
+}
+
 template <int W>
 int launch_ar(const ArParams& P, int grid, cudaStream_t st) {
   allreduce_kernel<W><<<grid, MPB_COMM_THREADS, 0, st>>>(P);
@@ -389,6 +443,30 @@ MPB_API int mpb_allreduce_fused(void* const* grads, void* const* params, void* c
     case 7: return launch_ar<7>(P, blocks, st);
     default: return launch_ar<8>(P, blocks, st);
   }
+}
+
+// In-place average of W symmetric bf16 buffers of n elements (n a multiple of 8*W).
+MPB_API int mpb_allreduce_bf16(void* const* bufs, void* const* pads, void* epochs, long long n, int rank, int W, int blocks,
+                               void* stream) {
+  if (W < 1 || W > MPB_MAX_WORLD || n <= 0 || (n % (8 * W)) != 0) return -1;
+  if (blocks < 1) blocks = 1;
+  if (blocks > MPB_MAX_COMM_BLOCKS) blocks = MPB_MAX_COMM_BLOCKS;
+  Bf16Params P;
+  memset(&P, 0, sizeof(P));
+  for (int i = 0; i < W; ++i) { P.bufs.p[i] = bufs[i]; P.pads.p[i] = pads[i]; }
+  P.epochs = (uint32_t*)epochs; P.n8 = n / 8; P.rank = rank; P.W = W; P.scale = 1.f / (float)W;
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (W) {
+    case 1: allreduce_bf16_kernel<1><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 2: allreduce_bf16_kernel<2><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 3: allreduce_bf16_kernel<3><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 4: allreduce_bf16_kernel<4><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 5: allreduce_bf16_kernel<5><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 6: allreduce_bf16_kernel<6><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 7: allreduce_bf16_kernel<7><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    default: allreduce_bf16_kernel<8><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+  }
+  return (int)cudaGetLastError();
 }
 
 MPB_API int mpb_broadcast(void* const* bufs, void* const* pads, void* epochs, long long n_floats, int rank, int W,

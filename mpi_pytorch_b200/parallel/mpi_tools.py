@@ -14,6 +14,8 @@ from __future__ import annotations
 import weakref
 from typing import Any, Dict, Optional
 
+import os
+
 import numpy as np
 import torch
 import torch.nn as nn
@@ -90,14 +92,28 @@ def mpi_broadcast(x: torch.Tensor, root: int = 0) -> torch.Tensor:
     return x
 
 
+def _wire_dtype(params) -> torch.dtype:
+    """Gradient wire format: ``MPB_GRAD_DTYPE`` (``fp32`` | ``bf16``) if set; otherwise bf16 when every parameter is
+    bf16 (the exchange then moves 2 bytes per element and accumulates in fp32 inside the kernel), else fp32."""
+    want = os.environ.get("MPB_GRAD_DTYPE", "").lower()
+    if want in ("bf16", "bfloat16"):
+        return torch.bfloat16
+    if want in ("fp32", "float32"):
+        return torch.float32
+    if params and all(p.dtype == torch.bfloat16 for p in params):
+        return torch.bfloat16
+    return torch.float32
+
+
 class _GradAverager:
     def __init__(self, model: nn.Module, bucket_mb: float = 32.0):
         self.coll = _collectives()
         w = bootstrap.world()
         params = [p for p in model.parameters() if p.requires_grad]
         self.device = params[0].device if params else w.device
+        self.dtype = _wire_dtype(params)
         self.layout = FlatLayout(params, int(bucket_mb * 2 ** 20), w.size)
-        self.arena = alloc_arena(self.layout.total, torch.float32, self.device, self.coll.alloc)
+        self.arena = alloc_arena(self.layout.total, self.dtype, self.device, self.coll.alloc)
 
     @torch.no_grad()
     def average(self) -> None:
@@ -107,7 +123,7 @@ class _GradAverager:
             if p.grad is None:                       # unused this step: contributes zeros
                 v.zero_()
                 continue
-            if p.grad.data_ptr() != v.data_ptr() or p.grad.dtype != torch.float32:
+            if p.grad.data_ptr() != v.data_ptr() or p.grad.dtype != self.dtype:
                 src.append(p.grad)
                 dst.append(v)
                 rebind.append((p, v))
@@ -117,7 +133,7 @@ class _GradAverager:
             self.coll.all_reduce_avg_(self.layout.bucket_view(self.arena, b))
         self.coll.sync_stream()
         for p, v in rebind:
-            if p.grad.dtype == torch.float32:
+            if p.grad.dtype == self.dtype:
                 p.grad = v                            # next step accumulates straight into the arena
             else:
                 p.grad.copy_(v)

@@ -297,9 +297,24 @@ class PeerCollectives:
             raise RuntimeError("mpb_allreduce_fused failed: {}".format(rc))
 
     def all_reduce_avg_(self, view: torch.Tensor, algo: str = "auto") -> None:
+        if view.dtype == torch.bfloat16:
+            return self._all_reduce_avg_bf16(view)
         if view.dtype != torch.float32:
-            raise TypeError("peer all-reduce operates on fp32 arenas")
+            raise TypeError("peer all-reduce operates on fp32 or bf16 arenas")
         self._launch_ar(view, None, None, None, None, None, 1, algo)
+
+    def _all_reduce_avg_bf16(self, view: torch.Tensor) -> None:
+        """bf16 wire format: peers exchange 2 bytes per gradient element (fp32 accumulation inside the kernel)."""
+        n = view.numel()
+        if n % (8 * self.size) != 0:
+            raise ValueError("bf16 all-reduce range must be a multiple of 8 * world elements")
+        blocks = self._blocks(n // 2, 1)
+        rc = self.lib.mpb_allreduce_bf16(self._peer_ptrs(view), self._pads_arr, c_void_p(self.epochs.data_ptr()), c_ll(n),
+                                         c_int(self.rank), c_int(self.size), c_int(blocks),
+                                         c_void_p(torch.cuda.current_stream().cuda_stream))
+        self.launches += 1
+        if rc != 0:
+            raise RuntimeError("mpb_allreduce_bf16 failed: {}".format(rc))
 
     def all_reduce_update_(self, grads, params, state: Dict[str, torch.Tensor], shadow, hyper: Hyper, step: int,
                            algo: str = "auto") -> None:

@@ -50,6 +50,20 @@ def main():
         e2 = (sh.float() - p.bfloat16().float()).abs().max().item()
         ok &= err < 1e-5 and e2 == 0
         results["checks"].append({"op": "adam", "n": n, "algo": algo, "max_err": err, "shadow_err": e2})
+    # bf16 wire format: fp32 accumulation in rank order, one rounding
+    for n in (4096, 1 << 20, 8 << 20):
+        n = n // (8 * W) * (8 * W)
+        gb = pc.alloc(n, torch.bfloat16)
+        torch.manual_seed(200 + r)
+        gb.copy_(torch.randn(n, device=w.device))
+        want = gb.float()
+        dist.all_reduce(want)
+        want = (want / W).bfloat16()
+        pc.all_reduce_avg_(gb)
+        torch.cuda.synchronize(); dist.barrier()
+        err = (gb.float() - want.float()).abs().max().item()
+        ok &= err <= 2e-2                                  # at most one bf16 ulp of an O(1) value (summation order)
+        results["checks"].append({"op": "avg_bf16", "n": n, "max_err": err})
     # broadcast
     b = pc.alloc(1 << 18, torch.float32)
     b.fill_(float(r + 1))
@@ -81,6 +95,23 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
             bus = 2 * (W - 1) / W * n * 4 / (ms.item() * 1e-3) / 1e9
             results["bandwidth"].append({"impl": name, "MB": mb, "us": ms.item() * 1e3, "bus_GBs": bus})
+    for mb in (8, 32, 128):                                # bf16 all-reduce: same element counts as the fp32 rows
+        n = int(mb * 2 ** 20 / 4) // (8 * W) * (8 * W)
+        gb = pc.alloc(n, torch.bfloat16)
+        tb = torch.empty(n, device=w.device, dtype=torch.bfloat16)
+        for name, fn in (("peer_bf16", lambda: pc.all_reduce_avg_(gb)), ("nccl_bf16", lambda: dist.all_reduce(tb))):
+            for _ in range(5):
+                fn()
+            torch.cuda.synchronize(); dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(20):
+                fn()
+            e1.record(); e1.synchronize()
+            ms = torch.tensor([e0.elapsed_time(e1) / 20], device=w.device)
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            results["bandwidth"].append({"impl": name, "MB_fp32_equiv": mb, "us": ms.item() * 1e3,
+                                         "bus_GBs": 2 * (W - 1) / W * n * 2 / (ms.item() * 1e-3) / 1e9})
     flag = torch.tensor([1 if ok else 0], device=w.device)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if r == 0:

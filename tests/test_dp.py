@@ -122,6 +122,27 @@ def test_mpi_tools_surface_2_ranks():
         assert torch.equal(m0, m1)
 
 
+def _avg_bf16_worker(w):
+    from mpi_pytorch_b200.parallel import mpi_tools
+    torch.manual_seed(0)
+    model = _tiny().to(torch.bfloat16)
+    mpi_tools.sync_params(model)
+    x = torch.full((2, 3, 8, 8), float(w.rank + 1), dtype=torch.bfloat16)
+    model(x).sum().backward()
+    local = [p.grad.clone() for p in model.parameters()]
+    mpi_tools.mpi_avg_grads(model)
+    return local, [p.grad.clone() for p in model.parameters()], mpi_tools._AVERAGERS[model].dtype
+
+
+def test_mpi_avg_grads_bf16_wire_2_ranks():
+    """An all-bf16 model exchanges its gradients in bf16 (2 bytes per element on the wire)."""
+    (l0, a0, d0), (l1, a1, d1) = run_ranks(_avg_bf16_worker, 2)
+    assert d0 == d1 == torch.bfloat16
+    for g0, g1, m0, m1 in zip(l0, l1, a0, a1):
+        assert m0.dtype == torch.bfloat16 and torch.equal(m0, m1)
+        assert torch.allclose(m0.float(), (g0.float() + g1.float()) / 2, rtol=2e-2, atol=1e-3)
+
+
 def test_mpi_tools_single_process_noop():
     from mpi_pytorch_b200.parallel import mpi_tools
     m = _tiny()
