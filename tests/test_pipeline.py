@@ -40,7 +40,9 @@ def _source_fixed(i0, i1):
 
 
 def _worker(w, labels):
-    pipe = EvalPipeline(w, N, RAW, OUT, _source_fixed, labels, _model_fn, micro_batch=5, seed=3)
+    from mpi_pytorch_b200.parallel.collectives import make_collectives
+    coll = make_collectives(w) if w.size > 2 else None      # also cover the collectives-object count reduction (K13)
+    pipe = EvalPipeline(w, N, RAW, OUT, _source_fixed, labels, _model_fn, micro_batch=5, seed=3, collectives=coll)
     return pipe.run(), int(pipe.seen)
 
 
