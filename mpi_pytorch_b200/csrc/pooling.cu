@@ -194,6 +194,61 @@ __global__ void __launch_bounds__(256, sizeof(T) == 2 ? 4 : 2) maxpool3x3_fwd_ke
   }
 }
 
+// bf16 specialisation of the 3x3 forward: the generic kernel spends ~600 instructions per thread on per-element
+// compare / NaN / byte-insert chains.  Here the maximum is taken with packed bf16x2 max (4 instructions per tap for 8
+// channels) and the argmax is recovered in a second pass, taps 8..0, with one packed equality mask and one LOP3 select
+// per channel pair -- "first maximum wins" as in torch.  (A NaN makes the max NaN and leaves argmax 0.)
+__global__ void __launch_bounds__(256) maxpool3x3_fwd_bf16_kernel(const __nv_bfloat16* __restrict__ x,
+                                                                  __nv_bfloat16* __restrict__ y,
+                                                                  unsigned char* __restrict__ idx, PoolGeom g) {
+  const int cvecs = g.C / 8;
+  const long long total = (long long)g.N * g.Ho * g.Wo * cvecs;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const unsigned iu = (unsigned)i;
+    const int cv = (int)(iu % (unsigned)cvecs);
+    unsigned t = iu / (unsigned)cvecs;
+    const int wo = (int)(t % (unsigned)g.Wo); t /= (unsigned)g.Wo;
+    const int ho = (int)(t % (unsigned)g.Ho);
+    const int n = (int)(t / (unsigned)g.Ho);
+    const int h0 = ho * g.sh - g.ph, w0 = wo * g.sw - g.pw;
+    uint4 raw[9];
+    unsigned okmask = 0;
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int h = h0 + r, w = w0 + s;
+        raw[r * 3 + s] = make_uint4(0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u);      // -inf
+        if (h >= 0 && h < g.H && w >= 0 && w < g.W) {
+          okmask |= 1u << (r * 3 + s);
+          raw[r * 3 + s] = *reinterpret_cast<const uint4*>(x + (((long long)n * g.H + h) * g.W + w) * g.C + cv * 8);
+        }
+      }
+    uint4 mx = raw[0];
+    __nv_bfloat162* m = reinterpret_cast<__nv_bfloat162*>(&mx);
+#pragma unroll
+    for (int p = 1; p < 9; ++p) {
+      const __nv_bfloat162* v = reinterpret_cast<const __nv_bfloat162*>(&raw[p]);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) m[k] = __hmax2_nan(m[k], v[k]);
+    }
+    unsigned id[4] = {0u, 0u, 0u, 0u};                       // two 16-bit tap indices per channel pair
+#pragma unroll
+    for (int p = 8; p >= 0; --p) {
+      if (!((okmask >> p) & 1u)) continue;
+      const __nv_bfloat162* v = reinterpret_cast<const __nv_bfloat162*>(&raw[p]);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const unsigned eq = __heq2_mask(v[k], m[k]);
+        id[k] = (eq & ((unsigned)p * 0x00010001u)) | (~eq & id[k]);
+      }
+    }
+    const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
+    *reinterpret_cast<uint4*>(y + o) = mx;
+    if (idx) *reinterpret_cast<uint2*>(idx + o) = make_uint2(__byte_perm(id[0], id[1], 0x6420), __byte_perm(id[2], id[3], 0x6420));
+  }
+}
+
 // 3x3 / stride 2 / pad 1 on even H, W (the ResNet / DenseNet stem pool): one thread owns a 2x2 quad of input pixels.
 // The quad (2a..2a+1, 2b..2b+1) is covered by exactly the four windows (a..a+1, b..b+1), so four (argmax, dy) loads
 // produce four outputs -- the per-pixel formulation needs nine loads for the same four pixels.
@@ -428,7 +483,11 @@ MPB_API int mpb_maxpool_fwd(const void* x, void* y, unsigned char* idx, int N, i
   const PoolGeom g = geom(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw);
   const long long total = (long long)N * Ho * Wo * (C / 8);
   if (kh == 3 && kw == 3) {
-    DISPATCH_T(dtype, maxpool3x3_fwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, g);)
+    if (dtype == MPB_BF16) {
+      maxpool3x3_fwd_bf16_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, idx, g);
+    } else {
+      maxpool3x3_fwd_kernel<float><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const float*)x, (float*)y, idx, g);
+    }
   } else {
     DISPATCH_T(dtype, maxpool_fwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, g);)
   }
