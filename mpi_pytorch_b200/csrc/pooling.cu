@@ -367,6 +367,84 @@ __global__ void __launch_bounds__(256) avgpool_kernel(const T* __restrict__ in, 
   }
 }
 
+// Windows up to 3x3 (Inception's 3x3/1 branch pools, DenseNet's 2x2/2 transitions): 32-bit index arithmetic and all tap
+// loads issued before the first add.  The generic kernel above decodes with 64-bit div/mod and walks the window with
+// a dependent load per tap.
+template <typename T, bool BWD>
+__global__ void __launch_bounds__(256) avgpool_k3_kernel(const T* __restrict__ in, T* __restrict__ out, PoolGeom g,
+                                                         int count_include_pad) {
+  const int cvecs = g.C / 8;
+  const unsigned total = (unsigned)((long long)g.N * (BWD ? g.H * g.W : g.Ho * g.Wo) * cvecs);
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int cv = (int)(i % (unsigned)cvecs);
+    unsigned t = i / (unsigned)cvecs;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (!BWD) {
+      const int wo = (int)(t % (unsigned)g.Wo); t /= (unsigned)g.Wo;
+      const int ho = (int)(t % (unsigned)g.Ho);
+      const int n = (int)(t / (unsigned)g.Ho);
+      const int h0 = ho * g.sh - g.ph, w0 = wo * g.sw - g.pw;
+      const int h1 = min(h0 + g.kh, g.H + g.ph), w1 = min(w0 + g.kw, g.W + g.pw);
+      const int ch0 = max(h0, 0), cw0 = max(w0, 0), ch1 = min(h1, g.H), cw1 = min(w1, g.W);
+      const float inv = 1.f / (float)(count_include_pad ? (h1 - h0) * (w1 - w0) : (ch1 - ch0) * (cw1 - cw0));
+      Raw8<T> raw[9];
+      bool ok[9];
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int s2 = 0; s2 < 3; ++s2) {
+          const int h = h0 + r, w = w0 + s2;
+          ok[r * 3 + s2] = r < g.kh && s2 < g.kw && h >= 0 && h < g.H && w >= 0 && w < g.W;
+          if (ok[r * 3 + s2]) load_raw(in + (((long long)n * g.H + h) * g.W + w) * g.C + cv * 8, raw[r * 3 + s2]);
+        }
+#pragma unroll
+      for (int p = 0; p < 9; ++p) {
+        if (!ok[p]) continue;
+        float v[8];
+        unpack(raw[p], v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += v[k];
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] *= inv;
+    } else {
+      const int w = (int)(t % (unsigned)g.W); t /= (unsigned)g.W;
+      const int h = (int)(t % (unsigned)g.H);
+      const int n = (int)(t / (unsigned)g.H);
+      int ho_lo = (h + g.ph - g.kh + g.sh) / g.sh; if (h + g.ph - g.kh + 1 <= 0) ho_lo = 0;
+      int wo_lo = (w + g.pw - g.kw + g.sw) / g.sw; if (w + g.pw - g.kw + 1 <= 0) wo_lo = 0;
+      const int ho_hi = min((h + g.ph) / g.sh, g.Ho - 1), wo_hi = min((w + g.pw) / g.sw, g.Wo - 1);
+      Raw8<T> raw[9];
+      float scale[9];
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+          const int ho = ho_lo + a, wo = wo_lo + b;
+          const int h0 = ho * g.sh - g.ph, w0 = wo * g.sw - g.pw;
+          const bool covers = ho <= ho_hi && wo <= wo_hi && h >= h0 && h < h0 + g.kh && w >= w0 && w < w0 + g.kw;
+          scale[a * 3 + b] = 0.f;
+          if (covers) {
+            const int h1 = min(h0 + g.kh, g.H + g.ph), w1 = min(w0 + g.kw, g.W + g.pw);
+            const int cnt = count_include_pad ? (h1 - h0) * (w1 - w0)
+                                              : (min(h1, g.H) - max(h0, 0)) * (min(w1, g.W) - max(w0, 0));
+            scale[a * 3 + b] = 1.f / (float)cnt;
+            load_raw(in + (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8, raw[a * 3 + b]);
+          }
+        }
+#pragma unroll
+      for (int p = 0; p < 9; ++p) {
+        if (scale[p] == 0.f) continue;
+        float v[8];
+        unpack(raw[p], v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = fmaf(v[k], scale[p], acc[k]);
+      }
+    }
+    store8(out + (size_t)i * 8, acc);
+  }
+}
+
 __device__ __forceinline__ int ada_start(int o, int in, int out) { return (int)(((long long)o * in) / out); }
 __device__ __forceinline__ int ada_end(int o, int in, int out) { return (int)((((long long)(o + 1)) * in + out - 1) / out); }
 
@@ -515,6 +593,14 @@ MPB_API int mpb_avgpool(const void* in, void* out, int N, int H, int W, int C, i
   const PoolGeom g = geom(N, H, W, C, Ho, Wo, kh, kw, sh, sw, ph, pw);
   const long long total = (long long)N * (backward ? (long long)H * W : (long long)Ho * Wo) * (C / 8);
   cudaStream_t st = (cudaStream_t)stream;
+  // windows up to 3x3 whose backward needs at most 3x3 covering windows (kernel <= 3 * stride), 32-bit element count
+  const bool k3 = kh <= 3 && kw <= 3 && kh <= 3 * sh && kw <= 3 * sw && total < (1ll << 31);
+  if (k3) {
+    DISPATCH_T(dtype, if (backward) avgpool_k3_kernel<T, true><<<grid_for(total, 256), 256, 0, st>>>((const T*)in, (T*)out, g, count_include_pad);
+               else avgpool_k3_kernel<T, false><<<grid_for(total, 256), 256, 0, st>>>((const T*)in, (T*)out, g, count_include_pad);)
+    MPB_CHECK_LAUNCH();
+    return 0;
+  }
   DISPATCH_T(dtype, if (backward) avgpool_kernel<T, true><<<grid_for(total, 256), 256, 0, st>>>((const T*)in, (T*)out, g, count_include_pad);
              else avgpool_kernel<T, false><<<grid_for(total, 256), 256, 0, st>>>((const T*)in, (T*)out, g, count_include_pad);)
   MPB_CHECK_LAUNCH();
