@@ -209,6 +209,7 @@ MPB_API int mpb_bn_stats(const void* x, float* sums, long long M, int C, int dty
   if (C % 8 != 0 || C > 2048) return -1;
   cudaStream_t st = (cudaStream_t)stream;
   MPB_CUDA(cudaMemsetAsync(sums, 0, 2 * C * sizeof(float), st));
+  if (mpbbn::stream_ok(M, C, dtype)) return mpbbn::stream_stats(x, sums, M, C, st);
   const Map mp = make_map(C);
   const int grid = rows_grid(M, mp.rows_per_block, 4);
   const size_t smem = (size_t)mp.threads * 16 * sizeof(float);

@@ -97,6 +97,34 @@ __global__ void __launch_bounds__(256) bns_fwd_kernel(Inputs<2> in, int nin, bf1
   }
 }
 
+// Per-channel sum and sum of squares (BatchNorm statistics of a tensor that did not come out of one of our conv
+// epilogues: DenseNet's concatenated features, a conv-bias gradient).  sums must be zero on entry.
+__global__ void __launch_bounds__(256) bns_stats_kernel(Inputs<1> in, int nin, float* __restrict__ sums, const StreamGeom g) {
+  BNS_PROLOGUE(1)
+  float s0[8] = {0}, s1[8] = {0};
+  for (int i = 0; i < mine; ++i) {
+    BNS_CHUNK(1)
+    for (int r = r0; r < rows_here; r += g.rows_per_block) {
+      float v[8];
+      unpack8(*reinterpret_cast<const uint4*>(base + ((size_t)r * g.C + cv * 8) * 2), v);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { s0[k] += v[k]; s1[k] = fmaf(v[k], v[k], s1[k]); }
+    }
+    BNS_RELEASE(1)
+  }
+  float* red = reinterpret_cast<float*>(smem);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { red[t * 16 + k] = s0[k]; red[t * 16 + 8 + k] = s1[k]; }
+  __syncthreads();
+  for (int u = t; u < g.cvecs * 16; u += blockDim.x) {
+    const int c8 = u >> 4, k = u & 15;
+    float s = 0.f;
+    for (int r = 0; r < g.rows_per_block; ++r) s += red[(r * g.cvecs + c8) * 16 + k];
+    if (k < 8) atomicAdd(sums + c8 * 8 + k, s);
+    else atomicAdd(sums + g.C + c8 * 8 + (k - 8), s);
+  }
+}
+
 // mask_mode: 0 = no ReLU, 1 = ReLU mask from the saved output z (input 2), 2 = mask recomputed from x
 __global__ void __launch_bounds__(256) bns_reduce_kernel(Inputs<3> in, int nin, const float* __restrict__ gamma,
                                                          const float* __restrict__ beta, const float* __restrict__ save_mean,
@@ -227,6 +255,18 @@ int stream_fwd(const void* x, const void* res, void* out, const float* sums, con
   bns_fwd_kernel<<<grid_for_chunks(g.nchunks, 3), g.threads, smem, st>>>(in, nin, (bf16*)out, sums, gamma, beta, run_mean,
                                                                          run_var, save_mean, save_invstd, num_batches, g,
                                                                          eps, momentum, relu, training);
+  return (int)cudaGetLastError();
+}
+
+int stream_stats(const void* x, float* sums, long long M, int C, cudaStream_t st) {
+  const StreamGeom g = make_geom(M, C);
+  Inputs<1> in;
+  in.p[0] = (const bf16*)x;
+  int smem = kStages * g.chunk_elems * 2;
+  if (smem < g.threads * 16 * 4) smem = g.threads * 16 * 4;
+  static bool configured = false;
+  if (!configured) { int rc = set_smem(bns_stats_kernel, 200 * 1024); if (rc) return rc; configured = true; }
+  bns_stats_kernel<<<grid_for_chunks(g.nchunks, 4), g.threads, smem, st>>>(in, 1, sums, g);
   return (int)cudaGetLastError();
 }
 

@@ -95,6 +95,7 @@ bool stream_ok(long long M, int C, int dtype);
 int stream_fwd(const void* x, const void* res, void* out, const float* sums, const float* gamma, const float* beta,
                float* run_mean, float* run_var, float* save_mean, float* save_invstd, long long* num_batches, long long M,
                int C, float eps, float momentum, int relu, int training, cudaStream_t st);
+int stream_stats(const void* x, float* sums, long long M, int C, cudaStream_t st);
 int stream_bwd(const void* dz, const void* z, const void* x, const float* gamma, const float* beta, const float* save_mean,
                const float* save_invstd, float* dsum, void* dx, void* dres, float* dgamma, float* dbeta, long long M, int C,
                int mask_mode, int accumulate, cudaStream_t st);
