@@ -109,6 +109,9 @@ def _gemm():
 class _ConvFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, stride, padding, dilation, groups, want_stats):
+        # the (non-differentiable) statistics output would otherwise get a materialised zeros gradient: one tiny
+        # fill launch per convolution per step
+        ctx.set_materialize_grads(False)
         x = _nhwc(x)
         w = _compute_weight(weight, x.dtype)
         ctx.save_for_backward(x, w)
@@ -138,6 +141,8 @@ class _ConvFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, gy, *unused):
+        if gy is None:
+            return (None,) * 8
         x, w = ctx.saved_tensors
         stride, padding, dilation, groups, has_bias, wdtype = ctx.conf
         gy = _nhwc(gy)
