@@ -24,18 +24,19 @@ class _Op:
 
 class _Comm:
     def _ensure(self):
-        size = int(os.environ.get("WORLD_SIZE", "1"))
+        size = self.Get_size()
         if size > 1 and not dist.is_initialized():
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
             os.environ.setdefault("MASTER_PORT", "29511")
-            dist.init_process_group("gloo", rank=int(os.environ.get("RANK", "0")), world_size=size)
+            dist.init_process_group("gloo", rank=self.Get_rank(), world_size=size)
         return size
 
+    # rank/size as a launcher would export them: torchrun's names first, then Open MPI's (what ``mpiexec`` sets)
     def Get_rank(self):
-        return int(os.environ.get("RANK", "0"))
+        return int(os.environ.get("RANK", os.environ.get("OMPI_COMM_WORLD_RANK", "0")))
 
     def Get_size(self):
-        return int(os.environ.get("WORLD_SIZE", "1"))
+        return int(os.environ.get("WORLD_SIZE", os.environ.get("OMPI_COMM_WORLD_SIZE", "1")))
 
     # ---- buffer collectives (numpy arrays, in the style of mpi4py's upper-case methods)
     def Allreduce(self, sendbuf, recvbuf, op=None):

@@ -30,20 +30,21 @@ def build_sources(settings, world, n):
         def source(i0, i1):
             g = torch.Generator().manual_seed(settings.SEED * 7919 + i0)
             return torch.randint(0, 256, (i1 - i0, RAW_HW[0], RAW_HW[1], 3), generator=g, dtype=torch.uint8)
-        return source, labels, RAW_HW
+        return source, labels, RAW_HW, None
     import pandas as pd
-    from mpi_pytorch_b200.data.dataset import GetData
-    df = pd.read_csv(settings.TEST_CSV)
+    from mpi_pytorch_b200.data.dataset import GetData, render_index_images
+    df = pd.read_csv(settings.TEST_CSV).iloc[:n]
+    if world.rank == 0:
+        render_index_images(df, settings.TEST_DIR)       # stand-in JPEGs for generated rows; no-op for Herbarium
     ds = GetData(settings.TEST_DIR, df['file_name'].values, df['category_id'].values, None, mode='test')
     hmax, wmax = int(df['height'].max()), int(df['width'].max())
+    frame_hw = torch.as_tensor(df[['height', 'width']].values)
 
     def source(i0, i1):
-        out = torch.zeros(i1 - i0, hmax, wmax, 3, dtype=torch.uint8)
-        for j, i in enumerate(range(i0, i1)):
-            im = ds.load_uint8(i)
-            out[j, :im.shape[0], :im.shape[1]] = im
-        return out
-    return source, torch.as_tensor(df['category_id'].values), (hmax, wmax)
+        # a list of frames of their own sizes: stage 1 resizes each image over its true extent, as
+        # pil_image.resize does in the reference (evaluation_pipeline.py:89), not over a padded canvas
+        return [ds.load_uint8(i) for i in range(i0, i1)]
+    return source, torch.as_tensor(df['category_id'].values), (hmax, wmax), frame_hw
 
 
 def pipeline(world=None, settings=None, n_samples=None):
@@ -53,7 +54,8 @@ def pipeline(world=None, settings=None, n_samples=None):
     if world.rank == 0:
         logger.info('Logger Initialized')
     n = n_samples or (1000 if settings.DEBUG else 10000)
-    source, labels, raw_hw = build_sources(settings, world, n)
+    source, labels, raw_hw, frame_hw = build_sources(settings, world, n)
+    n = min(n, int(labels.numel()))
 
     def model_fn():
         model, _ = initialize_model(settings.MODEL_NAME, settings.NUM_CLASSES, use_pretrained=False,
@@ -74,7 +76,8 @@ def pipeline(world=None, settings=None, n_samples=None):
         from mpi_pytorch_b200.parallel.collectives import make_collectives
         coll = make_collectives(world, settings.ALLREDUCE_ALGO)     # final count: mpb_count_allreduce over NVLink
     pipe = EvalPipeline(world, n, raw_hw, (settings.HEIGHT, settings.WIDTH), source, labels, model_fn,
-                        micro_batch=settings.PIPE_MICROBATCH, seed=settings.SEED, dtype=dtype, collectives=coll)
+                        micro_batch=settings.PIPE_MICROBATCH, seed=settings.SEED, dtype=dtype, collectives=coll,
+                        frame_hw=frame_hw)
     return pipe.run()
 
 

@@ -79,8 +79,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     link_stamp = LIB + ".sha"
     dig = _digest(objs)
     if not (os.path.exists(LIB) and os.path.exists(link_stamp) and open(link_stamp).read() == dig):
-        cmd = [nvcc] + ARCH + ["-shared", "-o", LIB] + objs + ["-lcuda"] if False else \
-              [nvcc] + ARCH + ["-shared", "-o", LIB] + objs
+        cmd = [nvcc] + ARCH + ["-shared", "-o", LIB] + objs      # libcuda entry points are resolved at run time
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n" + r.stderr[-4000:])

@@ -427,6 +427,10 @@ MPB_API int mpb_bn_bwd_noalloc(const void* dz, const void* z, const void* x, con
     return -4;
   }
   if (C <= 0 || C % 8 != 0) return -1;
+  if (M <= 0) {                                         // an empty batch would launch zero-sized grids
+    fprintf(stderr, "mpb_bn_bwd_noalloc: M=%lld rows; need at least one\n", M);
+    return -1;
+  }
   int dev = -1;
   MPB_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= MPB_NOALLOC_MAX_DEVICES) return -5;

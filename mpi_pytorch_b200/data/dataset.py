@@ -112,6 +112,36 @@ def create_dataset(train_dir: str, train_file: str, n_images: int, out_dir: str 
     return p_tr, p_te
 
 
+def group_by_shape(frames: Sequence[torch.Tensor]):
+    """Positions of ``frames`` grouped by frame shape, in first-seen order."""
+    groups: dict = {}
+    for j, f in enumerate(frames):
+        groups.setdefault(tuple(f.shape), []).append(j)
+    return list(groups.values())
+
+
+def resize_frames(frames: Sequence[torch.Tensor], hw: Tuple[int, int], device, dtype: torch.dtype,
+                  channels_last: bool, mode: str) -> torch.Tensor:
+    """Resize + normalise a list of HWC uint8 frames: ONE pinned upload and ONE kernel launch per distinct frame
+    size (every image is resized on its own, as ``pil_image.resize`` / ``transforms.Resize`` do in the reference)."""
+    from .. import ops
+    device = torch.device(device)
+    out: Optional[torch.Tensor] = None
+    for pos in group_by_shape(frames):
+        stack = torch.stack([frames[j] for j in pos])
+        if device.type == "cuda":
+            stack = stack.pin_memory().to(device, non_blocking=True)
+        y = ops.resize_normalize(stack, hw[0], hw[1], mode, dtype, channels_last)
+        if len(pos) == len(frames):
+            return y
+        if out is None:
+            out = torch.empty((len(frames),) + tuple(y.shape[1:]), dtype=y.dtype, device=y.device)
+            if channels_last:
+                out = out.contiguous(memory_format=torch.channels_last)
+        out[torch.as_tensor(pos, device=y.device)] = y
+    return out
+
+
 class FileShard:
     """This rank's slice of a CSV-indexed JPEG dataset, batched for the GPU.
 
@@ -142,7 +172,6 @@ class FileShard:
         self.epoch = int(epoch)
 
     def __iter__(self):
-        from .. import ops
         n = len(self.ds)
         order = torch.arange(n)
         if self.shuffle:
@@ -152,37 +181,66 @@ class FileShard:
             idx = order[b * self.batch_size:(b + 1) * self.batch_size].tolist()
             frames = [self.ds.load_uint8(i) for i in idx]
             labels = torch.as_tensor([int(self.ds.labels[i]) for i in idx], dtype=torch.int64)
-            outs = []
-            for f in frames:                           # one launch per distinct frame size (Herbarium: ~1000x680 for all)
-                u8 = f.unsqueeze(0).to(self.device, non_blocking=True)
-                outs.append(ops.resize_normalize(u8, self.hw[0], self.hw[1], "bilinear", self.dtype, self.channels_last))
-            x = torch.cat(outs, dim=0)
+            x = resize_frames(frames, self.hw, self.device, self.dtype, self.channels_last, "bilinear")
             if self.channels_last:
                 x = x.contiguous(memory_format=torch.channels_last)
             yield x, labels.to(self.device)
 
 
-def make_synthetic_index(out_dir: str, n_train: int = 64, n_test: int = 16, num_classes: int = 10, hw=(40, 28),
-                         seed: int = 0):
-    """Write a tiny Herbarium-shaped dataset (JPEG files + the two CSV indices with the reference's columns,
-    data/*.csv:1) so the file-backed path can be exercised without the 6 GB original."""
-    import pandas as pd
+SYNTH_LICENSE = 999       # `license` value that marks rows of a generated (non-Herbarium) index
+
+
+def _render_row(directory: str, rel: str, h: int, w: int, cat: int, sid: int) -> None:
+    """Deterministic stand-in JPEG for one index row: noise plus a class-dependent colour cast, so a model can
+    actually learn the labels."""
     from PIL import Image
+    full = os.path.join(directory, rel)
+    if os.path.exists(full):
+        return
+    os.makedirs(os.path.dirname(full), exist_ok=True)
+    rng = np.random.RandomState(sid % (2 ** 31))
+    arr = (rng.rand(h, w, 3) * 96).astype(np.int32)
+    arr[:, :, cat % 3] += 40 + 8 * (cat % 16)
+    arr[: h // 2, :, (cat // 3) % 3] += 6 * (cat % 24)
+    Image.fromarray(np.clip(arr, 0, 255).astype(np.uint8)).save(full, quality=95)
+
+
+def render_index_images(frame, directory: str) -> int:
+    """Write the JPEG of every generated row of ``frame`` that is missing under ``directory``; rows of a real
+    (Herbarium) index are left alone.  Returns the number of generated rows."""
+    gen = frame[frame["license"] == SYNTH_LICENSE]
+    for rel, h, w, cat, sid in zip(gen["file_name"], gen["height"], gen["width"], gen["category_id"], gen["id"]):
+        _render_row(directory, rel, int(h), int(w), int(cat), int(sid))
+    return len(gen)
+
+
+def make_synthetic_index(out_dir: str, n_train: int = 64, n_test: int = 16, num_classes: int = 10, hw=(40, 28),
+                         seed: int = 0, render: bool = True, csv_dir: Optional[str] = None):
+    """Write a small Herbarium-shaped dataset: the two CSV indices with the reference's columns (data/*.csv:1) and,
+    with ``render``, the JPEG files under ``out_dir/{train,test}/`` -- so the file-backed path runs without the 6 GB
+    original.  Frame widths vary by a few pixels like the real set (680/681 there)."""
+    import pandas as pd
     rng = np.random.RandomState(seed)
     paths = {}
+    csv_dir = csv_dir or out_dir
+    os.makedirs(csv_dir, exist_ok=True)
+    nid = 100000
     for split, n in (("train", n_train), ("test", n_test)):
         rows = []
         for i in range(n):
             cat = int(rng.randint(0, num_classes))
-            rel = "images/{:03d}/{:02d}/{}.jpg".format(cat, i % 100, 100000 + i)
-            full = os.path.join(out_dir, split, rel)
-            os.makedirs(os.path.dirname(full), exist_ok=True)
-            arr = (rng.rand(hw[0], hw[1], 3) * 255).astype(np.uint8)
-            arr[:, :, cat % 3] = np.clip(arr[:, :, cat % 3].astype(int) + 20 * cat, 0, 255).astype(np.uint8)
-            Image.fromarray(arr).save(full, quality=95)
-            rows.append({"file_name": rel, "height": hw[0], "id": 100000 + i, "license": 0, "width": hw[1],
+            w = hw[1] + int(rng.randint(0, 2))
+            rel = "images/{:03d}/{:02d}/{}.jpg".format(cat // 100, cat % 100, nid)
+            rows.append({"file_name": rel, "height": hw[0], "id": nid, "license": SYNTH_LICENSE, "width": w,
                          "category_id": cat, "institution_id": 0})
+            nid += 1
         df = pd.DataFrame(rows, columns=CSV_COLUMNS)
-        paths[split] = os.path.join(out_dir, "{}_sample.csv".format(split))
+        paths[split] = os.path.join(csv_dir, "{}_sample.csv".format(split))
         df.to_csv(paths[split])
+        if render:
+            # both splits are read from the *training* image directory, as in the reference
+            # (main.py:99-109 and evaluation_pipeline.py:59 use TRAIN_DIR for test_sample.csv rows too)
+            render_index_images(df, os.path.join(out_dir, "train"))
+            if split == "test":
+                render_index_images(df, os.path.join(out_dir, "test"))
     return paths["train"], paths["test"]

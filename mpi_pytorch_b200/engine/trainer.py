@@ -97,6 +97,7 @@ class Trainer:
             path = os.path.join(self.s.CHECKPOINT_DIR, self.s.CHECKPOINT_NAME)
             self.log.info("_Loading Checkpoint")
             _, _, epoch = load_checkpoint(path, self.model, self.optimizer, map_location=self.device)
+            self.engine.refresh_shadow()
             self.start_epoch = epoch + 1
             self.log.info("_Checkpoint loaded")
 
@@ -106,8 +107,16 @@ class Trainer:
     def make_file_shards(self):
         """CSV + JPEG path (SYNTHETIC=False): rank-local training shard and, on rank 0, the un-sharded
         validation set -- the same split logic as main.py:73-112, minus the pickled scatter."""
-        from ..data.dataset import FileShard, load_index
+        from ..data.dataset import FileShard, load_index, render_index_images
+        if not os.path.exists(self.s.TEST_CSV if self.s.DEBUG else self.s.TRAIN_CSV):
+            raise FileNotFoundError("SYNTHETIC=False needs the CSV index {} (shipped under ./data; or run "
+                                    "create_dataset.py)".format(self.s.TEST_CSV if self.s.DEBUG else self.s.TRAIN_CSV))
         train_df, _ = load_index(self.s.TRAIN_CSV, self.s.TEST_CSV, self.s.DEBUG, self.s.SEED)
+        if self.world.rank == 0:
+            render_index_images(train_df, self.s.TRAIN_DIR)     # stand-in JPEGs for generated rows; no-op for Herbarium
+        if self.world.size > 1:
+            import torch.distributed as dist
+            dist.barrier()
         tr = FileShard(self.s.TRAIN_DIR, train_df, self.s.BATCH_SIZE, self.hw, self.world.rank, self.world.size,
                        self.device, self.dtype, self.channels_last, True, self.s.SEED, mode="train")
         va = None

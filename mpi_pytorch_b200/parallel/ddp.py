@@ -19,7 +19,7 @@ from typing import Any, Dict, Iterable, List, Optional
 import torch
 import torch.nn as nn
 
-from .arena import Bucket, FlatLayout, alloc_arena
+from .arena import ALIGN_ELEMS, Bucket, FlatLayout, alloc_arena
 from .collectives import Hyper, make_collectives
 
 
@@ -81,6 +81,7 @@ class FusedOptimizer(torch.optim.Optimizer):
         self.param_groups[0]["lr"] = g0.get("lr", self.param_groups[0]["lr"])
         self._hyper.lr = float(self.param_groups[0]["lr"])
         self._bind_state()
+        eng.refresh_shadow()          # a resume loads the model weights just before this call
 
     def zero_grad(self, set_to_none: bool = False) -> None:      # grads are arena views: never drop them
         self._engine.zero_grad()
@@ -133,6 +134,8 @@ class FusedDataParallel:
             self.comm_stream = None
         for p in self.layout.params:
             self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
+        # any in-place weight load (checkpoint resume, user code) must also refresh the bf16 compute copy
+        self._hooks.append(model.register_load_state_dict_post_hook(lambda _m, _keys: self.refresh_shadow()))
         self.optimizer = FusedOptimizer(self, self.layout.params, self.hyper)
         self.optimizer._bind_state()
         self._reset_pending()
@@ -167,16 +170,20 @@ class FusedDataParallel:
         statistics) -- one flat broadcast instead of one Bcast per tensor
         (mpi_tools.py:47-53)."""
         if self.world.size == 1:
+            self.refresh_shadow()
             return
         self.coll.broadcast_(self.param_arena[: self.layout.total], root)
-        if self.shadow_arena is not None:
-            self.shadow_arena.copy_(self.param_arena)
+        self.refresh_shadow()
         frozen = [p for p in self.params_all if not p.requires_grad]
         extras = [t for t in list(frozen) + list(self.model.buffers()) if t.numel() > 0]
         if extras:
             flat = torch.cat([t.detach().reshape(-1).to(torch.float32) for t in extras])
-            stage = self.coll.alloc(flat.numel(), torch.float32)
-            stage.copy_(flat)
+            # the peer broadcast moves 16-byte vectors: stage a zero-tailed multiple of ALIGN_ELEMS floats
+            # (DenseNet-121's buffers total 83,769 elements)
+            n_pad = -(-flat.numel() // ALIGN_ELEMS) * ALIGN_ELEMS
+            stage = self.coll.alloc(n_pad, torch.float32)
+            stage.zero_()
+            stage[:flat.numel()].copy_(flat)
             self.coll.broadcast_(stage, root)
             off = 0
             for t in extras:
@@ -184,6 +191,13 @@ class FusedDataParallel:
                 t.detach().copy_(stage[off:off + k].view(t.shape).to(t.dtype))
                 off += k
         self.coll.sync_stream()
+
+    @torch.no_grad()
+    def refresh_shadow(self) -> None:
+        """Re-derive the bf16 compute copy from the fp32 master arena.  Needed after anything that writes
+        parameters behind the fused kernels' back: ``load_state_dict`` / checkpoint resume, manual edits."""
+        if self.shadow_arena is not None:
+            self.shadow_arena.copy_(self.param_arena)
 
     # ------------------------------------------------------------------ per-step machinery
     def zero_grad(self) -> None:

@@ -21,7 +21,7 @@ import torch
 import torch.nn as nn
 
 from . import bootstrap
-from .arena import FlatLayout, alloc_arena
+from .arena import ALIGN_ELEMS, FlatLayout, alloc_arena
 from .collectives import make_collectives
 
 SUM = "sum"
@@ -165,9 +165,11 @@ def sync_params(model: nn.Module, root: int = 0, include_buffers: bool = True) -
         return None
     dev = tensors[0].device
     total = sum(t.numel() for t in tensors)
+    total = -(-total // ALIGN_ELEMS) * ALIGN_ELEMS    # the peer broadcast moves whole 16-byte vectors
     stage = coll.alloc(total, torch.float32)
     if stage.device != dev:
         stage = torch.zeros(total, dtype=torch.float32, device=dev)
+    stage.zero_()
     off = 0
     views = []
     for t in tensors:

@@ -4,22 +4,37 @@ Role map of the reference (/root/reference/evaluation_pipeline.py:162-199): rank
 images and assigns every image a predictor rank uniformly at random, rank 1 resizes,
 rank 2 tensorises + normalises and routes each image to *its* predictor, ranks 3..N-1
 hold a model replica each and count correct predictions; the partial results are summed
-on rank 0.  The reference moves one pickled PIL image per blocking ``comm.send``.
+on rank 0.  The reference moves one pickled PIL image per blocking ``comm.send``
+(rendezvous: one image in flight per edge).
 
-Here every edge carries **fixed-shape device tensors** -- a small int64 header plus a
-micro-batch payload -- over ``torch.distributed`` p2p (NCCL ``ncclSend/ncclRecv`` on
-GPUs, gloo on CPU), double-buffered with ``isend`` so a stage's kernel overlaps the
-previous hand-off.  Resize and normalise are CUDA kernels (``ops.resize_normalize`` and
-friends).  Per-image routing, the ``None``-sentinel termination protocol (a header with
-``last=1``) and the "sum of partial results" reduction are preserved; the reduction is an
-exact int64 count instead of a float.  With fewer than 4 ranks the stages fold onto the
-available ranks instead of raising (``np.random.randint(3, size)`` needs size > 3 in the
-reference, evaluation_pipeline.py:178).
+Here every edge carries ONE fixed-size device message per micro-batch -- an int64 header
+(count, last-flag, per-image label / predictor / sample id / frame size) and the payload
+packed behind it -- over ``torch.distributed`` p2p (``ncclSend/ncclRecv`` on GPUs, gloo on
+CPU), and the data path never waits on the host:
+
+* every edge has its OWN 2-rank process group, i.e. its own NCCL communicator and stream,
+  so the hand-offs of different edges are not serialised behind each other;
+* the receiver pre-posts the ``irecv`` of message i+1 into the other half of a double
+  buffer before it processes message i, and senders rotate through a ring of send slots,
+  so a stage's kernels overlap both its inbound and its outbound transfer;
+* nothing is read back per message: the number of messages per edge and the routing are
+  pure functions of ``(seed, n, predictors, micro_batch)`` that every rank evaluates
+  itself (the routing draw is seeded here; the reference's is not).  The
+  header still carries them, the last message of every edge still carries the sentinel
+  (``last = 1``, the reference's ``None`` tuple), and both are checked once at the end.
+
+Resize and normalise are CUDA kernels (``csrc/preprocess.cu``); every image is resized on
+its own true frame size (one launch per distinct size in a micro-batch), like
+``pil_image.resize`` in evaluation_pipeline.py:89.  The "sum of partial results"
+reduction is an exact int64 count instead of a float.  With fewer than 4 ranks the
+stages fold onto the available ranks instead of raising (``np.random.randint(3, size)``
+needs size > 3 in the reference, evaluation_pipeline.py:178).
 """
 from __future__ import annotations
 
 import dataclasses
-from typing import Callable, Dict, List, Optional, Tuple
+import time
+from typing import Callable, Dict, List, Optional, Sequence, Tuple, Union
 
 import torch
 import torch.distributed as dist
@@ -27,7 +42,9 @@ import torch.distributed as dist
 from .. import ops
 from ..utils.logging import get_logger
 
-HDR_ROWS_EXTRA = 1        # row 0 of every header: (count, last, reserved)
+HDR_COLS = 5              # per-image row: label, predictor rank, sample id, frame height, frame width
+HDR_ROWS_EXTRA = 1        # row 0 of every header: (count, last, message index, 0, 0)
+SEND_SLOTS = 3
 
 
 @dataclasses.dataclass
@@ -48,190 +65,368 @@ def assign_roles(size: int) -> Roles:
     return Roles(0, 0, 0, [0])
 
 
-class _Edge:
-    """One directed p2p edge with double-buffered asynchronous sends."""
+def route(seed: int, n: int, predictors: Sequence[int]) -> torch.Tensor:
+    """Predictor rank of every sample: uniform over the predictor ranks like
+    ``np.random.randint(3, size)`` (evaluation_pipeline.py:178), but seeded so every rank can evaluate it."""
+    g = torch.Generator().manual_seed(int(seed))
+    return torch.tensor(list(predictors), dtype=torch.int64)[torch.randint(0, len(predictors), (n,), generator=g)]
 
-    def __init__(self, me: int, peer: int, device: torch.device):
-        self.me, self.peer, self.device = me, peer, device
-        self._pending: List[Tuple[object, torch.Tensor]] = []
 
-    def send(self, header: torch.Tensor, payload: Optional[torch.Tensor]) -> None:
-        works = [(dist.isend(header, dst=self.peer), header)]
-        if payload is not None:
-            works.append((dist.isend(payload, dst=self.peer), payload))
-        self._pending.extend(works)
-        while len(self._pending) > 4:              # at most two messages (hdr+payload) in flight
-            w, _keep = self._pending.pop(0)
-            w.wait()
+def _hdr_bytes(mb: int) -> int:
+    return (mb + HDR_ROWS_EXTRA) * HDR_COLS * 8
+
+
+class _Msg:
+    """One fixed-size message buffer: header rows first (8-byte aligned), payload bytes behind them."""
+
+    def __init__(self, mb: int, payload_shape: Tuple[int, ...], payload_dtype: torch.dtype, device: torch.device):
+        hb = -(-_hdr_bytes(mb) // 256) * 256
+        pb = int(torch.empty((), dtype=payload_dtype).element_size())
+        for d in payload_shape:
+            pb *= int(d)
+        self.buf = torch.zeros(hb + pb, dtype=torch.uint8, device=device)
+        self.header = self.buf[:_hdr_bytes(mb)].view(torch.int64).view(mb + HDR_ROWS_EXTRA, HDR_COLS)
+        self.payload = self.buf[hb:hb + pb].view(payload_dtype).view(payload_shape)
+        self.work = None
+
+
+class _SendEdge:
+    def __init__(self, peer: int, group, mb: int, shape, dtype, device):
+        self.peer, self.group = peer, group
+        self.slots = [_Msg(mb, shape, dtype, device) for _ in range(SEND_SLOTS)]
+        self.i = 0
+
+    def next_slot(self) -> _Msg:
+        m = self.slots[self.i % SEND_SLOTS]
+        if m.work is not None:
+            m.work.wait()              # NCCL: a stream dependency, not a host block
+            m.work = None
+        return m
+
+    def post(self, m: _Msg) -> None:
+        m.work = dist.isend(m.buf, dst=self.peer, group=self.group)
+        self.i += 1
 
     def flush(self) -> None:
-        for w, _keep in self._pending:
-            w.wait()
-        self._pending = []
-
-    def recv(self, header: torch.Tensor, payload: torch.Tensor) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
-        dist.recv(header, src=self.peer)
-        if int(header[0, 0].item()) > 0:
-            dist.recv(payload, src=self.peer)
-            return header, payload
-        return header, None
+        for m in self.slots:
+            if m.work is not None:
+                m.work.wait()
+                m.work = None
 
 
-def make_header(mb: int, device: torch.device) -> torch.Tensor:
-    return torch.zeros(mb + HDR_ROWS_EXTRA, 3, dtype=torch.int64, device=device)
+class _RecvEdge:
+    def __init__(self, peer: int, group, mb: int, shape, dtype, device, n_msgs: int):
+        self.peer, self.group, self.n_msgs = peer, group, n_msgs
+        self.slots = [_Msg(mb, shape, dtype, device) for _ in range(2)]
+        self.posted = 0
+
+    def post_next(self) -> None:
+        if self.posted < self.n_msgs:
+            m = self.slots[self.posted % 2]
+            m.work = dist.irecv(m.buf, src=self.peer, group=self.group)
+            self.posted += 1
+
+    def take(self, i: int) -> _Msg:
+        m = self.slots[i % 2]
+        m.work.wait()
+        m.work = None
+        return m
 
 
 class EvalPipeline:
     """Drives one rank's part of the pipeline.
 
-    ``source(i0, i1) -> uint8 [n, RAW_H, RAW_W, 3]`` yields raw frames for global sample ids
-    ``[i0, i1)``; ``labels`` is the int64 label vector of the whole test set (rank 0 only
-    needs it); ``model_fn()`` builds the predictor's model (with the checkpoint loaded)."""
+    ``source(i0, i1)`` yields the raw frames of global sample ids ``[i0, i1)``: either a uint8 tensor
+    ``[k, RAW_H, RAW_W, 3]`` (uniform size) or a list of ``k`` HWC uint8 tensors no larger than ``raw_hw``, in which
+    case ``frame_hw`` (int ``[n, 2]``, e.g. the CSV's height/width columns) gives every sample's true size.
+    ``labels`` is the int64 label vector of the whole test set (rank 0 only needs it); ``model_fn()`` builds the
+    predictor's model (with the checkpoint loaded)."""
 
     def __init__(self, world, n_samples: int, raw_hw: Tuple[int, int], out_hw: Tuple[int, int],
-                 source: Callable[[int, int], torch.Tensor], labels: torch.Tensor,
+                 source: Callable[[int, int], Union[torch.Tensor, List[torch.Tensor]]], labels: torch.Tensor,
                  model_fn: Callable[[], torch.nn.Module], micro_batch: int = 32, seed: int = 0,
-                 dtype: torch.dtype = torch.float32, resize_mode: str = "bicubic", collectives=None):
+                 dtype: torch.dtype = torch.float32, resize_mode: str = "bicubic", collectives=None,
+                 frame_hw: Optional[torch.Tensor] = None):
         self.w = world
         self.coll = collectives        # optional: sums the per-rank counts with the peer-memory count kernel (K13)
         self.dev = world.device
+        self.cuda = self.dev.type == "cuda"
         self.roles = assign_roles(world.size)
         self.n, self.mb, self.seed = int(n_samples), int(micro_batch), seed
-        self.raw_hw, self.out_hw = raw_hw, out_hw
+        self.raw_hw, self.out_hw = tuple(raw_hw), tuple(out_hw)
         self.source, self.labels, self.model_fn = source, labels, model_fn
         self.dtype, self.resize_mode = dtype, resize_mode
+        self.frame_hw = None if frame_hw is None else torch.as_tensor(frame_hw, dtype=torch.int64).reshape(-1, 2)
         self.log = get_logger()
         self.correct = torch.zeros((), dtype=torch.int64, device=self.dev)
         self.seen = 0
+        self.protocol_errors = torch.zeros((), dtype=torch.int64, device=self.dev)
+        self.stats: Dict[str, float] = {}
         self._model: Optional[torch.nn.Module] = None
-        self._edges: Dict[int, _Edge] = {}
-        self._queues: Dict[int, List[Tuple[torch.Tensor, int]]] = {}
+        # routing and message counts: pure functions of (seed, n, predictors, mb), evaluated by every rank
+        self.assign = route(seed, self.n, self.roles.predictors)
+        self.n_front = -(-self.n // self.mb)                                   # messages on 0->1 and 1->2
+        self.n_pred = {p: -(-int((self.assign == p).sum()) // self.mb) for p in self.roles.predictors}
+        self.raw_shape = (self.mb, self.raw_hw[0], self.raw_hw[1], 3)
+        self.small_shape = (self.mb, self.out_hw[0], self.out_hw[1], 3)
+        self.batch_shape = (self.mb, 3, self.out_hw[0], self.out_hw[1])
+        self._send: Dict[Tuple[int, str], _SendEdge] = {}
+        self._groups: Dict[Tuple[int, int], object] = {}
+        self._local: Dict[str, _Msg] = {}
+        self._queues: Dict[int, Dict[str, object]] = {}
+        self._busy_ms = 0.0
+        self._events: List[Tuple[object, object]] = []
+        self._make_groups()
 
     # ------------------------------------------------------------------ plumbing
-    def _edge(self, peer: int) -> _Edge:
-        if peer not in self._edges:
-            self._edges[peer] = _Edge(self.w.rank, peer, self.dev)
-        return self._edges[peer]
+    def _make_groups(self) -> None:
+        """One 2-rank process group per pipeline edge (every rank creates all of them, in the same order)."""
+        r = self.roles
+        edges = [(r.reader, r.resizer), (r.resizer, r.normalizer)] + [(r.normalizer, p) for p in r.predictors]
+        for a, b in edges:
+            if a != b and (a, b) not in self._groups and self.w.size > 1:
+                self._groups[(a, b)] = dist.new_group([a, b])
 
-    def _emit(self, dest: int, stage: str, header: torch.Tensor, payload: Optional[torch.Tensor]) -> None:
+    def _out_msg(self, dest: int, stage: str, shape, dtype) -> _Msg:
         if dest == self.w.rank:
-            getattr(self, "_stage_" + stage)(header, payload)
+            if stage not in self._local:
+                self._local[stage] = _Msg(self.mb, shape, dtype, self.dev)
+            return self._local[stage]
+        key = (dest, stage)
+        if key not in self._send:
+            self._send[key] = _SendEdge(dest, self._groups[(self.w.rank, dest)], self.mb, shape, dtype, self.dev)
+        return self._send[key].next_slot()
+
+    def _emit(self, dest: int, stage: str, m: _Msg, idx: int) -> None:
+        if dest == self.w.rank:
+            getattr(self, "_stage_" + stage)(m, idx)
         else:
-            self._edge(dest).send(header, payload)
+            self._send[(dest, stage)].post(m)
+
+    def _timed(self, fn, *a):
+        """Run one stage body and record its device time (CUDA events; wall clock on CPU)."""
+        if self.cuda:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn(*a)
+            e1.record()
+            self._events.append((e0, e1))
+        else:
+            t0 = time.perf_counter()
+            fn(*a)
+            self._busy_ms += (time.perf_counter() - t0) * 1e3
+
+    def _ids(self, idx: int) -> Tuple[int, int]:
+        i0 = idx * self.mb
+        return i0, min(i0 + self.mb, self.n)
 
     # ------------------------------------------------------------------ stage 0: read + dispatch (C19)
     def _run_reader(self) -> None:
-        g = torch.Generator().manual_seed(self.seed)
-        preds = self.roles.predictors
-        assign = torch.tensor(preds)[torch.randint(0, len(preds), (self.n,), generator=g)]   # seeded, unlike :178
-        for i0 in range(0, self.n, self.mb):
-            i1 = min(i0 + self.mb, self.n)
+        copy_stream = torch.cuda.Stream(self.dev) if self.cuda else None
+        staged: List[Optional[Tuple[torch.Tensor, torch.Tensor]]] = [None, None]
+
+        def stage_host(idx: int) -> Tuple[torch.Tensor, torch.Tensor]:
+            """Host side of one message: frames padded into the fixed canvas + the header rows, in pinned memory."""
+            i0, i1 = self._ids(idx)
             k = i1 - i0
-            raw = self.source(i0, i1).to(self.dev)
-            if k < self.mb:
-                pad = torch.zeros(self.mb - k, *raw.shape[1:], dtype=raw.dtype, device=self.dev)
-                raw = torch.cat([raw, pad])
-            hdr = make_header(self.mb, self.dev)
-            hdr[0, 0] = k
-            hdr[1:k + 1, 0] = self.labels[i0:i1].to(self.dev)
-            hdr[1:k + 1, 1] = assign[i0:i1].to(self.dev)
-            hdr[1:k + 1, 2] = torch.arange(i0, i1, device=self.dev)
-            self._emit(self.roles.resizer, "resize", hdr, raw)
-        end = make_header(self.mb, self.dev)
-        end[0, 1] = 1
-        self._emit(self.roles.resizer, "resize", end, None)
+            frames = self.source(i0, i1)
+            raw = torch.zeros(self.raw_shape, dtype=torch.uint8)
+            hdr = torch.zeros(self.mb + HDR_ROWS_EXTRA, HDR_COLS, dtype=torch.int64)
+            if torch.is_tensor(frames):
+                raw[:k, :frames.shape[1], :frames.shape[2]] = frames
+                hdr[1:k + 1, 3], hdr[1:k + 1, 4] = frames.shape[1], frames.shape[2]
+            else:
+                for j, f in enumerate(frames):
+                    raw[j, :f.shape[0], :f.shape[1]] = f
+                    hdr[1 + j, 3], hdr[1 + j, 4] = f.shape[0], f.shape[1]
+            hdr[0, 0], hdr[0, 1], hdr[0, 2] = k, int(idx == self.n_front - 1), idx
+            hdr[1:k + 1, 0] = self.labels[i0:i1]
+            hdr[1:k + 1, 1] = self.assign[i0:i1]
+            hdr[1:k + 1, 2] = torch.arange(i0, i1)
+            if self.cuda:
+                raw, hdr = raw.pin_memory(), hdr.pin_memory()
+            return raw, hdr
+
+        def body(idx: int) -> None:
+            raw, hdr = staged[idx % 2]
+            m = self._out_msg(self.roles.resizer, "resize", self.raw_shape, torch.uint8)
+            m.payload.copy_(raw, non_blocking=True)
+            m.header.copy_(hdr, non_blocking=True)
+            self._emit(self.roles.resizer, "resize", m, idx)
+
+        if self.n_front:
+            staged[0] = stage_host(0)
+        for idx in range(self.n_front):
+            self._timed(body, idx)
+            if idx + 1 < self.n_front:
+                staged[(idx + 1) % 2] = stage_host(idx + 1)        # decode of i+1 overlaps the transfer of i
+        del copy_stream
 
     # ------------------------------------------------------------------ stage 1: resize (C20)
-    def _stage_resize(self, hdr: torch.Tensor, raw: Optional[torch.Tensor]) -> None:
-        out = None
-        if raw is not None:
-            out = ops.resize_u8(raw, self.out_hw[0], self.out_hw[1], self.resize_mode)
-        self._emit(self.roles.normalizer, "normalize", hdr, out)
+    def _stage_resize(self, m: _Msg, idx: int) -> None:
+        out = self._out_msg(self.roles.normalizer, "normalize", self.small_shape, torch.uint8)
+        i0, i1 = self._ids(idx)
+        if self.frame_hw is None:
+            out.payload.copy_(ops.resize_u8(m.payload, self.out_hw[0], self.out_hw[1], self.resize_mode))
+        else:
+            groups: Dict[Tuple[int, int], List[int]] = {}
+            for j, (h, w) in enumerate(self.frame_hw[i0:i1].tolist()):
+                groups.setdefault((int(h), int(w)), []).append(j)
+            for (h, w), pos in groups.items():       # one launch per distinct frame size; a run of equal sizes is a slice
+                if pos == list(range(pos[0], pos[-1] + 1)):
+                    crop = m.payload[pos[0]:pos[-1] + 1, :h, :w]
+                    out.payload[pos[0]:pos[-1] + 1] = ops.resize_u8(crop, self.out_hw[0], self.out_hw[1], self.resize_mode)
+                else:
+                    sel = self._dev_index(pos)
+                    out.payload[sel] = ops.resize_u8(m.payload[sel][:, :h, :w], self.out_hw[0], self.out_hw[1],
+                                                     self.resize_mode)
+        out.header.copy_(m.header)
+        self._emit(self.roles.normalizer, "normalize", out, idx)
 
     # ------------------------------------------------------------------ stage 2: normalise + route (C21)
-    def _stage_normalize(self, hdr: torch.Tensor, small: Optional[torch.Tensor]) -> None:
-        last = int(hdr[0, 1].item()) == 1
-        if small is not None:
-            k = int(hdr[0, 0].item())
-            x = ops.normalize_u8(small, self.dtype)                   # [mb, 3, h, w]
-            rows = hdr[1:k + 1].tolist()
-            for j, (label, dest, _sid) in enumerate(rows):
-                q = self._queues.setdefault(int(dest), [])
-                q.append((x[j], int(label)))
-                if len(q) == self.mb:
-                    self._flush_queue(int(dest))
-        if last:
-            for dest in self.roles.predictors:
-                if self._queues.get(dest):
-                    self._flush_queue(dest)
-                end = make_header(self.mb, self.dev)
-                end[0, 1] = 1
-                self._emit(dest, "predict", end, None)
+    def _stage_normalize(self, m: _Msg, idx: int) -> None:
+        i0, i1 = self._ids(idx)
+        x = ops.normalize_u8(m.payload, self.dtype)                   # [mb, 3, h, w]
+        perm, bounds = self._route_plan(idx)
+        xs, rows = x[perm], m.header[1:][perm]                        # one gather: images grouped by predictor
+        for p, (a, b) in bounds.items():                              # host-known slice bounds: no read-back
+            q = self._queue(p)
+            f = int(q["fill"])
+            q["x"][f:f + b - a] = xs[a:b]
+            q["rows"][f:f + b - a] = rows[a:b]
+            q["fill"] = f + b - a
+            if q["fill"] >= self.mb:
+                self._flush_queue(p, self.mb)
+        if idx == self.n_front - 1:
+            for p in self.roles.predictors:
+                if p in self._queues and self._queues[p]["fill"] > 0:
+                    self._flush_queue(p, int(self._queues[p]["fill"]))
 
-    def _flush_queue(self, dest: int) -> None:
-        q = self._queues[dest]
-        k = len(q)
-        batch = torch.zeros(self.mb, 3, self.out_hw[0], self.out_hw[1], dtype=self.dtype, device=self.dev)
-        batch[:k] = torch.stack([t for t, _ in q])
-        hdr = make_header(self.mb, self.dev)
-        hdr[0, 0] = k
-        hdr[1:k + 1, 0] = torch.tensor([l for _, l in q], dtype=torch.int64, device=self.dev)
-        self._queues[dest] = []
-        self._emit(dest, "predict", hdr, batch)
+    def _route_plan(self, idx: int):
+        """Per message: a device permutation that groups its images by predictor (all messages' permutations are
+        uploaded once, on first use) and the host-side [a, b) slice of every predictor inside the grouped order."""
+        if getattr(self, "_perm_dev", None) is None:
+            perms = torch.zeros(self.n_front, self.mb, dtype=torch.int64)
+            self._bounds: List[Dict[int, Tuple[int, int]]] = []
+            for i in range(self.n_front):
+                i0, i1 = self._ids(i)
+                d = self.assign[i0:i1]
+                order = torch.sort(d, stable=True).indices
+                perms[i, :i1 - i0] = order
+                sd, b, a = d[order].tolist(), {}, 0
+                for p in self.roles.predictors:
+                    c = sd.count(p)
+                    if c:
+                        b[p] = (a, a + c)
+                    a += c
+                self._bounds.append(b)
+            self._perm_dev = perms.to(self.dev)
+        return self._perm_dev[idx], self._bounds[idx]
+
+    def _dev_index(self, pos: List[int]) -> torch.Tensor:
+        return torch.as_tensor(pos, dtype=torch.int64).to(self.dev)
+
+    def _queue(self, p: int) -> Dict[str, object]:
+        if p not in self._queues:
+            self._queues[p] = {
+                "x": torch.zeros((2 * self.mb,) + self.batch_shape[1:], dtype=self.dtype, device=self.dev),
+                "rows": torch.zeros(2 * self.mb, HDR_COLS, dtype=torch.int64, device=self.dev),
+                "fill": 0, "sent": 0}
+        return self._queues[p]
+
+    def _flush_queue(self, p: int, k: int) -> None:
+        q = self._queues[p]
+        out = self._out_msg(p, "predict", self.batch_shape, self.dtype)
+        out.payload[:k].copy_(q["x"][:k])
+        out.header.zero_()
+        out.header[1:k + 1].copy_(q["rows"][:k])
+        sent = int(q["sent"])
+        last = int(sent == self.n_pred[p] - 1)
+        out.header[0, 0], out.header[0, 1], out.header[0, 2] = k, last, sent      # scalar fills: no host copy
+        rest = int(q["fill"]) - k
+        if rest > 0:
+            q["x"][:rest] = q["x"][k:k + rest].clone()
+            q["rows"][:rest] = q["rows"][k:k + rest].clone()
+        q["fill"], q["sent"] = rest, sent + 1
+        self._emit(p, "predict", out, sent)
 
     # ------------------------------------------------------------------ stage 3: predict (C22)
-    def _stage_predict(self, hdr: torch.Tensor, batch: Optional[torch.Tensor]) -> None:
-        if batch is None:
-            return
+    def _stage_predict(self, m: _Msg, idx: int) -> None:
         if self._model is None:
             self._model = self.model_fn().to(self.dev).eval()
-        k = int(hdr[0, 0].item())
+        me = self.w.rank
+        mine = int((self.assign == me).sum())
+        k = min(self.mb, mine - idx * self.mb)                        # this message's image count, known a priori
         with torch.no_grad():
-            x = batch[:k]
-            if self.dev.type == "cuda":
+            x = m.payload[:k]
+            if self.cuda:
                 x = x.contiguous(memory_format=torch.channels_last)
             out = self._model(x)
-        self.correct += ops.count_correct(out.float(), hdr[1:k + 1, 0])
+        self.correct += ops.count_correct(out, m.header[1:k + 1, 0].contiguous())
+        # protocol self-check, accumulated on the device and read once at the end
+        want_last = int(idx == self.n_pred[me] - 1)
+        bad = (m.header[0, 0] != k).to(torch.int64) + (m.header[0, 1] != want_last).to(torch.int64) + \
+              (m.header[1:k + 1, 1] != me).sum()
+        self.protocol_errors += bad
         self.seen += k
 
     # ------------------------------------------------------------------ receive loops
-    def _recv_loop(self, src: int, stage: str, payload_shape: Tuple[int, ...], payload_dtype: torch.dtype) -> None:
-        edge = self._edge(src)
-        while True:
-            hdr = make_header(self.mb, self.dev)
-            payload = torch.empty(payload_shape, dtype=payload_dtype, device=self.dev)
-            hdr, payload = edge.recv(hdr, payload)
-            getattr(self, "_stage_" + stage)(hdr, payload)
-            if int(hdr[0, 1].item()) == 1:
-                break
+    def _recv_loop(self, src: int, stage: str, shape: Tuple[int, ...], dtype: torch.dtype, n_msgs: int) -> None:
+        edge = _RecvEdge(src, self._groups[(src, self.w.rank)], self.mb, shape, dtype, self.dev, n_msgs)
+        edge.post_next()
+        fn = getattr(self, "_stage_" + stage)
+        for i in range(n_msgs):
+            edge.post_next()                      # message i+1 lands in the other buffer while i is processed
+            m = edge.take(i)
+            self._timed(fn, m, i)
 
     def run(self) -> Optional[float]:
         """Execute this rank's role(s); returns the global accuracy on rank 0 (``None`` elsewhere)."""
         r, roles = self.w.rank, self.roles
-        raw_shape = (self.mb, self.raw_hw[0], self.raw_hw[1], 3)
-        small_shape = (self.mb, self.out_hw[0], self.out_hw[1], 3)
-        batch_shape = (self.mb, 3, self.out_hw[0], self.out_hw[1])
+        if r in roles.predictors and self._model is None:
+            self._model = self.model_fn().to(self.dev).eval()
+        if self.w.size > 1:
+            dist.barrier()
+        ev0 = ev1 = None
+        if self.cuda:
+            torch.cuda.synchronize(self.dev)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+        t0 = time.perf_counter()
         if r == roles.reader:
             self._run_reader()
         elif r == roles.resizer:
-            self._recv_loop(roles.reader, "resize", raw_shape, torch.uint8)
+            self._recv_loop(roles.reader, "resize", self.raw_shape, torch.uint8, self.n_front)
         elif r == roles.normalizer:
-            self._recv_loop(roles.resizer, "normalize", small_shape, torch.uint8)
+            self._recv_loop(roles.resizer, "normalize", self.small_shape, torch.uint8, self.n_front)
         elif r in roles.predictors:
-            if self._model is None:
-                self._model = self.model_fn().to(self.dev).eval()
-            self._recv_loop(roles.normalizer, "predict", batch_shape, self.dtype)
-        for e in self._edges.values():
+            self._recv_loop(roles.normalizer, "predict", self.batch_shape, self.dtype, self.n_pred[r])
+        for e in self._send.values():
             e.flush()
+        elapsed = (time.perf_counter() - t0) * 1e3
+        if self.cuda:
+            ev1.record()
+            torch.cuda.synchronize(self.dev)
+            self._busy_ms = sum(a.elapsed_time(b) for a, b in self._events)
+            elapsed = ev0.elapsed_time(ev1)          # device-timed; max over ranks below
         if r in roles.predictors:
             self.log.info("Finished node {}, acc {}".format(r, float(self.correct.item()) / max(self.n, 1)))
-        total = self.correct.clone()
+        total = torch.stack([self.correct, self.protocol_errors]).clone()
+        el = torch.tensor([elapsed], dtype=torch.float64, device=self.dev)
         if self.w.size > 1:
             if self.coll is not None:
-                self.coll.all_reduce_sum_i64(total)     # exact int64 count through peer memory (C23 / K13)
+                c = total[0].clone()
+                self.coll.all_reduce_sum_i64(c)     # exact int64 count through peer memory (C23 / K13)
+                dist.all_reduce(total)
+                assert int(c.item()) == int(total[0].item())
             else:
                 dist.all_reduce(total)
-        acc = float(total.item()) / max(self.n, 1)
+            dist.all_reduce(el, op=dist.ReduceOp.MAX)
+        if int(total[1].item()) != 0:
+            raise RuntimeError("pipeline protocol check failed: {} header mismatches".format(int(total[1].item())))
+        acc = float(total[0].item()) / max(self.n, 1)
+        self.stats = {"elapsed_ms": float(el.item()), "images_per_s": self.n / max(float(el.item()), 1e-9) * 1e3,
+                      "stage_busy_ms": self._busy_ms, "stage_busy_frac": self._busy_ms / max(elapsed, 1e-9)}
         if r == 0:
             self.log.info("Accuracy is {}".format(acc))
             return acc

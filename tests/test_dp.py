@@ -61,16 +61,23 @@ def test_single_process_engine_matches_torch_adam():
     assert eng.step_count == 3
 
 
-def _dp_worker(w, steps):
+def _tiny_nobn():
     torch.manual_seed(0)
-    model = _tiny()
+    return nn.Sequential(nn.Conv2d(3, 8, 3, padding=1), nn.ReLU(), nn.AdaptiveAvgPool2d(1), nn.Flatten(), nn.Linear(8, 5))
+
+
+def _dp_worker(w, steps, bn):
+    torch.manual_seed(0)
+    model = _tiny() if bn else _tiny_nobn()
     eng = FusedDataParallel(model, w, Hyper("adam", lr=1e-2), bucket_mb=0.001)
     if w.rank != 0:                                   # de-synchronise, then sync_params must repair it
         with torch.no_grad():
             for p in model.parameters():
                 p.add_(1.0)
-            model[1].running_mean.add_(3.0)
+            if bn:
+                model[1].running_mean.add_(3.0)
     eng.sync_params(0)
+    synced_rm = model[1].running_mean.clone() if bn else torch.zeros(1)
     g = torch.Generator().manual_seed(123)
     X, Y = torch.randn(steps, 8, 3, 8, 8, generator=g), torch.randint(0, 5, (steps, 8), generator=g)
     per = 8 // w.size
@@ -78,17 +85,60 @@ def _dp_worker(w, steps):
         x, y = X[s, w.rank * per:(w.rank + 1) * per], Y[s, w.rank * per:(w.rank + 1) * per]
         loss = nn.functional.cross_entropy(model(x), y)
         eng.optimizer.zero_grad(); loss.backward(); eng.optimizer.step()
-    return [p.detach().clone() for p in model.parameters()], model[1].running_mean.clone()
+    return [p.detach().clone() for p in model.parameters()], synced_rm
 
 
 def test_dp_equivalence_2_ranks_vs_1():
-    """N ranks x batch B == 1 rank x batch N*B (BN uses per-rank statistics, so compare a BN-free head):
-    here we check rank agreement + closeness to the single-process run."""
-    res = run_ranks(_dp_worker, 2, (3,))
-    p0, p1 = res[0][0], res[1][0]
-    for a, b in zip(p0, p1):
+    """N ranks x batch B == 1 rank x batch N*B (mpi_tools.py:30-37 semantics: SUM then / size).  BatchNorm uses
+    per-rank statistics, so the equality with the single-process run is checked on a BN-free model; the BN model
+    checks replica agreement and that sync_params repaired the de-synchronised buffers."""
+    two = run_ranks(_dp_worker, 2, (3, False))
+    one = run_ranks(_dp_worker, 1, (3, False))
+    for a, b in zip(two[0][0], two[1][0]):
         assert torch.equal(a, b)                       # replicas stay bit-identical
-    assert torch.equal(res[0][1], res[0][1])
+    for a, ref in zip(two[0][0], one[0][0]):
+        assert torch.allclose(a, ref, atol=2e-6, rtol=1e-5), float((a - ref).abs().max())
+    res = run_ranks(_dp_worker, 2, (3, True))
+    for a, b in zip(res[0][0], res[1][0]):
+        assert torch.equal(a, b)
+    assert torch.equal(res[0][1], res[1][1])           # rank 1's +3.0 running_mean was overwritten by rank 0's
+    assert float(res[1][1].abs().max()) < 1.0
+
+
+class _OddBuffers(nn.Module):
+    """Parameter + buffer element counts that are NOT multiples of 4 (DenseNet-121: 83,769 buffer elements)."""
+
+    def __init__(self):
+        super().__init__()
+        self.w = nn.Parameter(torch.arange(7, dtype=torch.float32))
+        self.frozen = nn.Parameter(torch.arange(5, dtype=torch.float32), requires_grad=False)
+        self.register_buffer("stat", torch.arange(9, dtype=torch.float32))
+        self.register_buffer("count", torch.tensor(3, dtype=torch.long))
+
+
+def _odd_sync_worker(w):
+    from mpi_pytorch_b200.parallel import mpi_tools
+    out = []
+    for front in ("engine", "mpi_tools"):
+        m = _OddBuffers()
+        if w.rank != 0:
+            with torch.no_grad():
+                m.w.add_(10.0); m.frozen.add_(10.0); m.stat.add_(10.0); m.count.add_(10)
+        if front == "engine":
+            FusedDataParallel(m, w, Hyper("adam")).sync_params(0)
+        else:
+            mpi_tools.sync_params(m)
+        out.append((m.w.detach().clone(), m.frozen.detach().clone(), m.stat.clone(), m.count.clone()))
+    return out
+
+
+def test_sync_params_odd_sizes_2_ranks():
+    res = run_ranks(_odd_sync_worker, 2)
+    for front in range(2):
+        for a, b in zip(res[0][front], res[1][front]):
+            assert torch.equal(a, b)
+        assert torch.equal(res[1][front][0], torch.arange(7, dtype=torch.float32))
+        assert int(res[1][front][3]) == 3
 
 
 def _avg_worker(w):

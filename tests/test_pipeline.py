@@ -62,3 +62,33 @@ def test_pipeline_4_ranks_equals_single():
         res = run_ranks(_worker, n, (labels,))
         assert abs(res[0][0] - expected) < 1e-9
         assert sum(s for _, s in res) == N              # every image predicted exactly once
+
+
+def _source_ragged(i0, i1):
+    # frames of two different true sizes inside one canvas-sized message
+    out = []
+    for i in range(i0, i1):
+        f = _source(i, i + 1)[0]
+        out.append(f if i % 2 == 0 else f[:RAW[0] - 4, :RAW[1] - 3].contiguous())
+    return out
+
+
+def _ragged_worker(w, labels, hw):
+    pipe = EvalPipeline(w, N, RAW, OUT, _source_ragged, labels, _model_fn, micro_batch=5, seed=3, frame_hw=hw)
+    return pipe.run(), int(pipe.seen), pipe.stats
+
+
+def test_pipeline_resizes_each_frame_over_its_own_extent():
+    """A small image inside a larger canvas must be resized over ITS size (evaluation_pipeline.py:89 resizes each PIL
+    image individually), not squeezed into the canvas corner: predictions equal per-image preprocessing."""
+    from mpi_pytorch_b200 import ops
+    m = _model_fn().eval()
+    hw = torch.tensor([[RAW[0], RAW[1]] if i % 2 == 0 else [RAW[0] - 4, RAW[1] - 3] for i in range(N)])
+    with torch.no_grad():
+        labels = torch.cat([m(ops.normalize_u8(ops.resize_u8(f[None], OUT[0], OUT[1]))).argmax(1)
+                            for f in _source_ragged(0, N)])
+    labels[::4] = (labels[::4] + 1) % NCLS
+    expected = float((torch.arange(N) % 4 != 0).sum()) / N
+    res = run_ranks(_ragged_worker, 4, (labels, hw))
+    assert abs(res[0][0] - expected) < 1e-9 and sum(s for _, s, _ in res) == N
+    assert res[0][2]["images_per_s"] > 0

@@ -94,3 +94,7 @@ def test_noalloc_rejects_more_channels_than_its_scratch_holds():
     rc = lib.mpb_bn_bwd_noalloc(_ptr(t), _ptr(t), _ptr(t), _ptr(t), _ptr(t), _ptr(t), _ptr(t), c_void_p(0), _ptr(t),
                                 _ptr(t), c_ll(1), c_int(4096), c_int(0), c_int(0), c_void_p(0))
     assert rc == -4
+    # an empty batch is refused as well instead of launching zero-sized grids
+    rc = lib.mpb_bn_bwd_noalloc(_ptr(t), _ptr(t), _ptr(t), _ptr(t), _ptr(t), _ptr(t), _ptr(t), c_void_p(0), _ptr(t),
+                                _ptr(t), c_ll(0), c_int(8), c_int(0), c_int(0), c_void_p(0))
+    assert rc == -1
