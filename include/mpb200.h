@@ -178,6 +178,15 @@ int mpb_mc_create(long long bytes, int num_devices, int* fd_out, unsigned long l
 int mpb_mc_import(int fd, unsigned long long* mc_out);
 int mpb_mc_add_device(unsigned long long mc);
 int mpb_mc_bind_map(unsigned long long mc, unsigned long long mem_handle, long long bytes, void** mc_ptr);
+/* GRAD_DTYPE=bf16 form of mpb_allreduce_fused (same reference sites: mpi_tools.py:24-26,30-37 forces an fp32 wire,
+ * main.py:155): `grads` is this rank's local fp32 bucket, packed by the kernel into the symmetric bf16 `wire`
+ * buffers the peers read (2 bytes per element in the reduce-scatter), fp32 accumulation, Adam/SGD on the fp32
+ * masters, all-gather of params + bf16 shadow.  opt_kind 1|2, algo 1 (peer) | 2 (NVLS), n % (8*W) == 0.        */
+int mpb_allreduce_fused_bf16wire(const float* grads, void* const* wire, void* const* params, void* const* shadows,
+                                 void* const* pads, void* epochs, float* m, float* v, long long n, int rank, int W,
+                                 int algo, int blocks, int opt_kind, int step, float lr, float b1, float b2,
+                                 float eps, float wd, float momentum, const int* step_dev, void* mc_wire,
+                                 void* mc_params, void* mc_shadow, void* stream);
 /* in-place average of W symmetric bf16 buffers (n % (8*W) == 0): fp32 accumulation in rank order, one rounding */
 int mpb_allreduce_bf16(void* const* bufs, void* const* pads, void* epochs, long long n, int rank, int W, int blocks,
                        void* stream);

@@ -370,6 +370,124 @@ __global__ void __launch_bounds__(MPB_COMM_THREADS, 1) allreduce_bf16_kernel(Bf1
   if (threadIdx.x == 0) P.epochs[blockIdx.x] = e0 + 2;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// bf16 WIRE format inside the fused engine (GRAD_DTYPE=bf16).  wgrad keeps accumulating split-K partial sums in
+// the fp32 gradient arena; this kernel (1) packs its own fp32 bucket to a symmetric bf16 wire buffer, (2) after the
+// barrier reduces slice `rank` from every peer's wire buffer with fp32 accumulation in rank order -- 2 bytes per
+// element cross NVLink in the reduce-scatter instead of 4 -- (3) applies 1/W and Adam / SGD to the fp32 masters of
+// its slice and (4) all-gathers updated fp32 params + the bf16 compute copy by peer stores (or, algo 2, does (2)
+// with multimem.ld_reduce.acc::f32 bf16x2 through the switch and (4) with multimem.st).
+// The pack uses the same element -> block mapping as the reduce, so the per-block flag barrier is sufficient.
+struct WireParams {
+  const float* grads;           // local fp32 gradient bucket
+  PeerBufs wire;                // bf16* per rank (symmetric)
+  PeerBufs params, shadows, pads;
+  uint32_t* epochs;
+  float* m; float* v;
+  long long n;                  // multiple of 8*W
+  int rank, W, algo;            // 1 = peer loads/stores, 2 = NVLS
+  float scale;
+  __nv_bfloat16* mc_wire; float* mc_params; __nv_bfloat16* mc_shadow;
+  OptArgs opt;
+};
+
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+
+template <int W>
+__global__ void __launch_bounds__(MPB_COMM_THREADS, 1) allreduce_wire16_kernel(WireParams P) {
+  if (P.opt.kind != 0 && P.opt.step_ptr != nullptr) {
+    const int step = *P.opt.step_ptr;
+    P.opt.first_step = (step == 1);
+    P.opt.bc1 = 1.f - powf(P.opt.b1, (float)step);
+    P.opt.bc2_sqrt = sqrtf(1.f - powf(P.opt.b2, (float)step));
+  }
+  const uint32_t e0 = P.epochs[blockIdx.x];
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long nthreads = (long long)gridDim.x * blockDim.x;
+  const long long slice8 = (P.n / W) >> 3;
+  // (1) pack: fp32 -> bf16, my copy of every slice, element -> thread mapping identical to the reduce below
+  {
+    uint4* dst = reinterpret_cast<uint4*>(P.wire.p[P.rank]);
+    for (int q = 0; q < W; ++q)
+      for (long long j = tid; j < slice8; j += nthreads) {
+        const long long i8 = (long long)q * slice8 + j;
+        const float4 a = *reinterpret_cast<const float4*>(P.grads + i8 * 8);
+        const float4 b = *reinterpret_cast<const float4*>(P.grads + i8 * 8 + 4);
+        uint4 r;
+        __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+        h[0] = __floats2bfloat162_rn(a.x, a.y); h[1] = __floats2bfloat162_rn(a.z, a.w);
+        h[2] = __floats2bfloat162_rn(b.x, b.y); h[3] = __floats2bfloat162_rn(b.z, b.w);
+        dst[i8] = r;
+      }
+  }
+  rank_barrier(P.pads, P.rank, W, e0 + 1);
+  constexpr int U = (W <= 2) ? 4 : 2;
+  const long long base8 = slice8 * P.rank;
+  for (long long j0 = 0; j0 < slice8; j0 += nthreads * U) {
+    uint4 u[U][W];
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const long long j = j0 + (long long)k * nthreads + tid;
+      if (j < slice8) {
+        if (P.algo == 2) {
+          u[k][0] = multimem_ld_reduce_bf16x8(reinterpret_cast<const uint4*>(P.mc_wire) + base8 + j);
+        } else {
+#pragma unroll
+          for (int p = 0; p < W; ++p) u[k][p] = ld_peer_u4(reinterpret_cast<const uint4*>(P.wire.p[p]) + base8 + j);
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const long long j = j0 + (long long)k * nthreads + tid;
+      if (j >= slice8) continue;
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const int np = (P.algo == 2) ? 1 : W;
+#pragma unroll
+      for (int p = 0; p < W; ++p) {
+        if (p >= np) break;
+        const unsigned w[4] = {u[k][p].x, u[k][p].y, u[k][p].z, u[k][p].w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { acc[2 * i] += __uint_as_float(w[i] << 16); acc[2 * i + 1] += __uint_as_float(w[i] & 0xFFFF0000u); }
+      }
+      const long long i8 = base8 + j;
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+        const long long i4 = i8 * 2 + hh;
+        float4 s = make_float4(acc[4 * hh] * P.scale, acc[4 * hh + 1] * P.scale, acc[4 * hh + 2] * P.scale, acc[4 * hh + 3] * P.scale);
+        float* pp = reinterpret_cast<float*>(P.params.p[P.rank]) + i4 * 4;
+        float4 p4 = *reinterpret_cast<float4*>(pp);
+        float4 m4 = *reinterpret_cast<float4*>(P.m + i4 * 4);
+        float4 v4 = P.opt.kind == 1 ? *reinterpret_cast<float4*>(P.v + i4 * 4) : make_float4(0, 0, 0, 0);
+        p4.x = opt_one(p4.x, s.x, m4.x, v4.x, P.opt); p4.y = opt_one(p4.y, s.y, m4.y, v4.y, P.opt);
+        p4.z = opt_one(p4.z, s.z, m4.z, v4.z, P.opt); p4.w = opt_one(p4.w, s.w, m4.w, v4.w, P.opt);
+        *reinterpret_cast<float4*>(P.m + i4 * 4) = m4;
+        if (P.opt.kind == 1) *reinterpret_cast<float4*>(P.v + i4 * 4) = v4;
+        uint2 uu;
+        *reinterpret_cast<__nv_bfloat162*>(&uu.x) = __floats2bfloat162_rn(p4.x, p4.y);
+        *reinterpret_cast<__nv_bfloat162*>(&uu.y) = __floats2bfloat162_rn(p4.z, p4.w);
+        if (P.algo == 2) {
+          multimem_st_f4(P.mc_params + i4 * 4, p4);
+          if (P.mc_shadow) multimem_st_bf16x4(P.mc_shadow + i4 * 4, uu);
+        } else {
+#pragma unroll
+          for (int p = 0; p < W; ++p) {
+            st_peer_f4(reinterpret_cast<float*>(P.params.p[p]) + i4 * 4, p4);
+            if (P.shadows.p[p]) st_peer_u2(reinterpret_cast<__nv_bfloat16*>(P.shadows.p[p]) + i4 * 4, uu);
+          }
+        }
+      }
+    }
+  }
+  rank_barrier(P.pads, P.rank, W, e0 + 2);
+  if (threadIdx.x == 0) P.epochs[blockIdx.x] = e0 + 2;
+}
+
 template <int W>
 int launch_ar(const ArParams& P, int grid, cudaStream_t st) {
   allreduce_kernel<W><<<grid, MPB_COMM_THREADS, 0, st>>>(P);
@@ -443,6 +561,50 @@ MPB_API int mpb_allreduce_fused(void* const* grads, void* const* params, void* c
     case 7: return launch_ar<7>(P, blocks, st);
     default: return launch_ar<8>(P, blocks, st);
   }
+}
+
+// Fused reduce + optimizer with a bf16 wire format: `grads` is this rank's LOCAL fp32 bucket, `wire` the W symmetric
+// bf16 staging buffers (index = rank) the peers read; everything else as mpb_allreduce_fused.  n % (8*W) == 0,
+// opt_kind must be 1 or 2 (the averaged gradient itself is never materialised), algo 1 (peer) or 2 (NVLS).
+MPB_API int mpb_allreduce_fused_bf16wire(const float* grads, void* const* wire, void* const* params,
+                                         void* const* shadows, void* const* pads, void* epochs, float* m, float* v,
+                                         long long n, int rank, int W, int algo, int blocks, int opt_kind, int step,
+                                         float lr, float b1, float b2, float eps, float wd, float momentum,
+                                         const int* step_dev, void* mc_wire, void* mc_params, void* mc_shadow,
+                                         void* stream) {
+  if (W < 1 || W > MPB_MAX_WORLD || n <= 0 || (n % (8 * W)) != 0) return -1;
+  if (opt_kind != 1 && opt_kind != 2) return -1;
+  if (algo == 2 && (mc_wire == nullptr || mc_params == nullptr)) return -3;
+  if (algo != 2) algo = 1;
+  if (blocks < 1) blocks = 1;
+  if (blocks > MPB_MAX_COMM_BLOCKS) blocks = MPB_MAX_COMM_BLOCKS;
+  WireParams P;
+  memset(&P, 0, sizeof(P));
+  for (int i = 0; i < W; ++i) {
+    P.wire.p[i] = wire[i];
+    P.params.p[i] = params[i];
+    P.shadows.p[i] = shadows ? shadows[i] : nullptr;
+    P.pads.p[i] = pads[i];
+  }
+  P.grads = grads; P.epochs = (uint32_t*)epochs; P.m = m; P.v = v; P.n = n; P.rank = rank; P.W = W; P.algo = algo;
+  P.mc_wire = (__nv_bfloat16*)mc_wire; P.mc_params = (float*)mc_params; P.mc_shadow = (__nv_bfloat16*)mc_shadow;
+  P.scale = 1.f / (float)W;
+  P.opt.kind = opt_kind; P.opt.lr = lr; P.opt.b1 = b1; P.opt.b2 = b2; P.opt.eps = eps; P.opt.wd = wd;
+  P.opt.momentum = momentum; P.opt.first_step = (step == 1); P.opt.step_ptr = step_dev;
+  P.opt.bc1 = 1.f - powf(b1, (float)step);
+  P.opt.bc2_sqrt = sqrtf(1.f - powf(b2, (float)step));
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (W) {
+    case 1: allreduce_wire16_kernel<1><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 2: allreduce_wire16_kernel<2><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 3: allreduce_wire16_kernel<3><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 4: allreduce_wire16_kernel<4><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 5: allreduce_wire16_kernel<5><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 6: allreduce_wire16_kernel<6><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    case 7: allreduce_wire16_kernel<7><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+    default: allreduce_wire16_kernel<8><<<blocks, MPB_COMM_THREADS, 0, st>>>(P); break;
+  }
+  return (int)cudaGetLastError();
 }
 
 // In-place average of W symmetric bf16 buffers of n elements (n a multiple of 8*W).

@@ -82,13 +82,15 @@ class Trainer:
         self.model = model
         hyper = Hyper(kind=settings.OPTIMIZER, lr=settings.LR, momentum=settings.MOMENTUM)
         shadow = torch.bfloat16 if (self.dtype == torch.bfloat16 and ops.native_enabled()) else None
+        wire = torch.bfloat16 if str(settings.GRAD_DTYPE).lower() in ("bf16", "bfloat16") else torch.float32
         self.engine = FusedDataParallel(model, self.world, hyper, bucket_mb=settings.BUCKET_MB,
-                                        algo=settings.ALLREDUCE_ALGO, shadow_dtype=shadow)
+                                        algo=settings.ALLREDUCE_ALGO, shadow_dtype=shadow, grad_dtype=wire)
         self.optimizer = self.engine.optimizer
         self.start_epoch = 0
         self.autocast = (self.dtype == torch.bfloat16 and not ops.native_enabled())
         self._graph = None
         self._graph_static = None
+        self._graph_failed = False
         self.graph_launches_per_step = 0
 
     # ------------------------------------------------------------------ set-up helpers
@@ -186,7 +188,11 @@ class Trainer:
         captured once into a CUDA graph and replayed: one host call per step instead of ~600 launches
         (the eager step is host-bound on B200: ~18 ms of Python/launch overhead vs ~17 ms of kernels)."""
         if self._graph is None:
-            self._capture(images, labels)
+            try:
+                self._capture(images, labels)
+            except Exception:
+                self._graph_failed = True
+                raise
         sx, sy, sloss = self._graph_static
         sx.copy_(images, non_blocking=True)
         sy.copy_(labels, non_blocking=True)
@@ -194,21 +200,59 @@ class Trainer:
         self.engine.step_count += 1
         return sloss
 
+    def _step_for(self, images: torch.Tensor):
+        """The step function ``fit`` uses for a batch of this shape: the CUDA-graph replay for the shape the graph was
+        captured with (every full batch), the eager step for anything else (a ragged last batch) or when graphs are
+        switched off (``USE_CUDA_GRAPH=False`` / ``MPB_CUDA_GRAPH=0``) or not available (CPU)."""
+        if not (self.graph_capable() and getattr(self.s, "USE_CUDA_GRAPH", True)
+                and os.environ.get("MPB_CUDA_GRAPH", "1") != "0"):
+            return self.train_step
+        if self._graph is None:
+            if self._graph_failed or images.shape[0] != self.s.BATCH_SIZE:
+                return self.train_step
+            return self.train_step_graphed      # first full batch: two eager warm-up steps, capture, replay
+        return self.train_step_graphed if tuple(images.shape) == tuple(self._graph_static[0].shape) else self.train_step
+
     def _capture(self, images: torch.Tensor, labels: torch.Tensor) -> None:
+        """Warm up (allocator, lazily built tensor maps, autograd graph), then record one step.  The two warm-up steps
+        are real optimizer steps, so model / optimizer / BatchNorm state is saved before and put back after them: the
+        first replay is then exactly the first training step (``fit`` must not train its first batch three times)."""
         sx, sy = images.clone(), labels.clone()
+        eng = self.engine
+        with torch.no_grad():
+            eng.gather_optimizer_state()
+            saved_p = eng.param_arena.clone()
+            saved_s = {k: v.clone() for k, v in eng.state.items()}
+            saved_b = [b.detach().clone() for b in self.model.buffers()]
+            saved_frozen = [p.detach().clone() for p in eng.params_all if not p.requires_grad]
+            saved_step = eng.step_count
         cur = torch.cuda.current_stream(self.device)
         side = torch.cuda.Stream(self.device)
         side.wait_stream(cur)
         with torch.cuda.stream(side):
-            for _ in range(2):                       # warm-up on a side stream (real optimizer steps)
+            for _ in range(2):                       # warm-up on a side stream
                 self.train_step(sx, sy)
         cur.wait_stream(side)
+        with torch.no_grad():
+            eng.param_arena.copy_(saved_p)
+            for k, v in eng.state.items():
+                v.copy_(saved_s[k])
+            for b, sb in zip(self.model.buffers(), saved_b):
+                b.copy_(sb)
+            for p, sp in zip([p for p in eng.params_all if not p.requires_grad], saved_frozen):
+                p.copy_(sp)
+            eng.set_step(saved_step)
+            eng.refresh_shadow()
         torch.cuda.synchronize(self.device)
+        if self.world.size > 1:
+            import torch.distributed as dist
+            dist.barrier()                           # every rank restored before anyone's replay writes peers
         g = torch.cuda.CUDAGraph()
         n0 = count_launches(self.engine)
         with torch.cuda.graph(g):
             sloss = self.train_step(sx, sy)
         self.graph_launches_per_step = count_launches(self.engine) - n0     # our kernels inside one replay
+        self.engine.step_count = saved_step          # capture does not execute: no step was taken
         self._graph, self._graph_static = g, (sx, sy, sloss)
 
     @torch.no_grad()
@@ -251,7 +295,7 @@ class Trainer:
             tr_loss = torch.zeros((), dtype=torch.float32, device=self.device)
             with DeviceTimer(self.device) as t:
                 for images, labels in train:
-                    tr_loss += self.train_step(images, labels).float()
+                    tr_loss += self._step_for(images)(images, labels).float()
             nb = max(len(train), 1)
             local = float(tr_loss.item()) / nb
             secs = max_over_ranks(t.ms, self.device if w.backend == "nccl" else "cpu") / 1e3

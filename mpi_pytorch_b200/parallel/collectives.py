@@ -46,9 +46,14 @@ class TorchCollectives:
             view.mul_(1.0 / self.size)
 
     def all_reduce_update_(self, grads: torch.Tensor, params: torch.Tensor, state: Dict[str, torch.Tensor],
-                           shadow: Optional[torch.Tensor], hyper: Hyper, step: int, algo: str = "auto") -> None:
+                           shadow: Optional[torch.Tensor], hyper: Hyper, step: int, algo: str = "auto",
+                           wire: Optional[torch.Tensor] = None) -> None:
         """Average ``grads`` over ranks and apply one optimizer step to ``params`` (flat views).
-        Portable formulation: all-reduce, then the flat update as separate passes."""
+        Portable formulation: all-reduce, then the flat update as separate passes.  With ``wire`` (a bf16 staging
+        view) the exchange carries bf16 values: each rank's contribution is rounded once, the sum is fp32."""
+        if wire is not None:
+            wire.copy_(grads)
+            grads = wire.float()
         self.all_reduce_avg_(grads, algo)
         if hyper.kind == "adam":
             ref.adam_step(params, grads, state["exp_avg"], state["exp_avg_sq"], step, hyper.lr, hyper.beta1,

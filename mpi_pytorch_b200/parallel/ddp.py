@@ -98,7 +98,8 @@ class FusedDataParallel:
 
     def __init__(self, model: nn.Module, world, hyper: Optional[Hyper] = None, bucket_mb: float = 32.0,
                  algo: str = "auto", grad_dtype: torch.dtype = torch.float32,
-                 shadow_dtype: Optional[torch.dtype] = None, overlap: bool = True, collectives=None):
+                 shadow_dtype: Optional[torch.dtype] = None, overlap: bool = True, collectives=None,
+                 tail_bytes: Optional[int] = None):
         self.model, self.world = model, world
         self.device = world.device
         self.hyper = hyper or Hyper()
@@ -107,11 +108,17 @@ class FusedDataParallel:
         self.coll = collectives if collectives is not None else make_collectives(world, algo)
         model.to(self.device)
         self.params_all = list(model.parameters())
-        self.layout = FlatLayout(self.params_all, int(bucket_mb * 2 ** 20), world.size)
+        self.layout = FlatLayout(self.params_all, int(bucket_mb * 2 ** 20), world.size, tail_bytes=tail_bytes)
         n = self.layout.total
         dev = self.device
         self.param_arena = alloc_arena(n, torch.float32, dev, self.coll.alloc)
-        self.grad_arena = alloc_arena(n, grad_dtype if grad_dtype == torch.float32 else torch.float32, dev, self.coll.alloc)
+        # Gradients are always ACCUMULATED in fp32 (split-K wgrad adds partial sums into this arena).  With
+        # grad_dtype=bf16 the exchange itself is bf16: the fused kernel packs each bucket into `wire_arena`, peers
+        # read 2 bytes per element, sums are fp32 and the optimizer works on the fp32 masters.
+        self.grad_arena = alloc_arena(n, torch.float32, dev, self.coll.alloc)
+        self.wire_dtype = grad_dtype
+        self.wire_arena = alloc_arena(n, torch.bfloat16, dev, self.coll.alloc) \
+            if (grad_dtype == torch.bfloat16 and world.size > 1) else None
         self.shadow_arena = alloc_arena(n, shadow_dtype, dev, self.coll.alloc) if shadow_dtype is not None else None
         keys = ("exp_avg", "exp_avg_sq") if self.hyper.kind == "adam" else ("momentum_buffer",)
         self.state = {k: torch.zeros(max(n, 1), dtype=torch.float32, device=dev) for k in keys}
@@ -128,6 +135,7 @@ class FusedDataParallel:
         self._hooks = []
         self._in_flight: List[Bucket] = []
         self._state_sliced = False
+        self._suspended = False
         if self.device.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=dev)
         else:
@@ -212,18 +220,37 @@ class FusedDataParallel:
         p = self.layout.bucket_view(self.param_arena, b)
         st = {k: self.layout.bucket_view(v, b) for k, v in self.state.items()}
         sh = self.layout.bucket_view(self.shadow_arena, b) if self.shadow_arena is not None else None
+        kw = {"wire": self.layout.bucket_view(self.wire_arena, b)} if self.wire_arena is not None else {}
         step = self.step_count + 1
         if self.comm_stream is not None and self.overlap:
             self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self.comm_stream):
-                self.coll.all_reduce_update_(g, p, st, sh, self.hyper, step, b.algo)
+                self.coll.all_reduce_update_(g, p, st, sh, self.hyper, step, b.algo, **kw)
         else:
-            self.coll.all_reduce_update_(g, p, st, sh, self.hyper, step, b.algo)
+            self.coll.all_reduce_update_(g, p, st, sh, self.hyper, step, b.algo, **kw)
         if not self.coll.owns_full_state(b.algo):
             self._state_sliced = True
         self._in_flight.append(b)
 
+    def suspended(self):
+        """Context manager: run forward/backward with the engine detached -- gradients of THIS rank's batch stay in
+        the gradient arena, nothing is exchanged, no optimizer step is taken.  Used to check the fused path against
+        a plain all-reduce (bench.py ``dp_check``) and for gradient inspection."""
+        import contextlib
+
+        @contextlib.contextmanager
+        def _cm():
+            self._suspended = True
+            try:
+                yield self
+            finally:
+                self._suspended = False
+                self._reset_pending()
+        return _cm()
+
     def _on_grad(self, p: nn.Parameter) -> None:
+        if self._suspended:
+            return
         # Idempotent per step: a kernel that wrote p.grad in place reports completion explicitly, and autograd may
         # additionally run the post-accumulate hook for the same parameter (observed on B200 / torch 2.11).
         if id(p) in self._fired:

@@ -28,8 +28,34 @@ import torch.distributed as dist
 from ..build import lib_path
 from .collectives import Hyper
 
-ONESHOT_MAX_BYTES = 256 * 1024
+ONESHOT_MAX_BYTES = 256 * 1024      # fallback crossover when no measured table covers (world, bytes)
+ALGO_NAMES = {"oneshot": 0, "twoshot": 1, "nvls": 2}
+ALGO_TABLE_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "algo_table.json")
 c_void_p, c_int, c_ll, c_float = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+
+
+def load_algo_table(path: str = ALGO_TABLE_PATH) -> Dict[int, List[Tuple[int, str, int]]]:
+    """The measured per-(world, bucket bytes) choice of algorithm and grid, written by ``scripts/test_peer.py --sweep``
+    on the 8xB200 box: ``{"8": [[max_bytes, "oneshot|twoshot|nvls", blocks], ...]}`` with rows sorted by size; the
+    first row whose ``max_bytes`` covers the bucket wins, the last row covers everything larger."""
+    try:
+        import json
+        raw = json.load(open(path))
+        return {int(w): [(int(b), str(a), int(g)) for b, a, g in rows] for w, rows in raw.get("table", {}).items()}
+    except (OSError, ValueError, KeyError):
+        return {}
+
+
+def table_choice(table, world: int, nbytes: int, nvls: bool) -> Optional[Tuple[str, int]]:
+    rows = table.get(int(world))
+    if not rows:
+        return None
+    for max_bytes, algo, blocks in rows:
+        if nbytes <= max_bytes or (max_bytes, algo, blocks) == rows[-1]:
+            if algo == "nvls" and not nvls:
+                algo = "twoshot"
+            return algo, blocks
+    return None
 
 
 class _RawCuda:
@@ -105,6 +131,8 @@ class PeerCollectives:
         self.lib = ctypes.CDLL(lib_path())
         self.lib.mpb_oneshot_max_elems.restype = c_ll
         self.comm_blocks = comm_blocks
+        self.algo_table = load_algo_table() if os.environ.get("MPB_ALGO_TABLE", "1") != "0" else {}
+        self._ptr_cache: Dict[Tuple[int, int], object] = {}
         self.bufs: List[_SymBuf] = []
         self.launches = 0
         self.step_dev: Optional[torch.Tensor] = None    # device-resident optimizer step (set by the DP engine)
@@ -226,10 +254,15 @@ class PeerCollectives:
         if view is None:
             return None
         p = view.data_ptr()
+        hit = self._ptr_cache.get((p, 0))         # bucket views recur every step: build each pointer table once
+        if hit is not None:
+            return hit
         for b in self.bufs:
             if b.base <= p < b.base + b.nbytes:
                 off = p - b.base
-                return (c_void_p * self.size)(*[q + off for q in b.peers])
+                arr = (c_void_p * self.size)(*[q + off for q in b.peers])
+                self._ptr_cache[(p, 0)] = arr
+                return arr
         if self.size == 1:
             return (c_void_p * 1)(p)
         raise ValueError("tensor is not inside a symmetric arena obtained from PeerCollectives.alloc")
@@ -238,26 +271,45 @@ class PeerCollectives:
         if view is None:
             return 0
         p = view.data_ptr()
+        hit = self._ptr_cache.get((p, 1))
+        if hit is not None:
+            return hit
         for b in self.bufs:
             if b.mc and b.base <= p < b.base + b.nbytes:
+                self._ptr_cache[(p, 1)] = b.mc + (p - b.base)
                 return b.mc + (p - b.base)
         return 0
 
     # ------------------------------------------------------------------ collectives
-    def _algo(self, algo: str, nbytes: int, numel: int) -> int:
-        if algo == "oneshot":
-            a = 0
-        elif algo == "twoshot":
-            a = 1
-        elif algo == "nvls":
-            a = 2 if self.nvls else 1
-        elif self.nvls and nbytes > ONESHOT_MAX_BYTES:
-            a = 2
+    def _plan(self, algo: str, nbytes: int, numel: int) -> Tuple[int, int]:
+        """(algorithm id, grid) for one bucket.  ``algo`` may be a name, ``name:blocks`` (sweeps), or ``auto`` = the
+        measured table for this world size, falling back to the fixed crossover."""
+        blocks = 0
+        if ":" in algo:
+            algo, b = algo.split(":", 1)
+            blocks = int(b)
+        if algo in ALGO_NAMES:
+            a = ALGO_NAMES[algo]
+            if a == 2 and not self.nvls:
+                a = 1
         else:
-            a = 0 if nbytes <= ONESHOT_MAX_BYTES else 1
-        if a == 0 and numel > self.lib.mpb_oneshot_max_elems(c_int(self._blocks(numel, 0))):
+            pick = table_choice(self.algo_table, self.size, nbytes, self.nvls)
+            if pick is not None:
+                a, blocks = ALGO_NAMES[pick[0]], (blocks or pick[1])
+            elif self.nvls and nbytes > ONESHOT_MAX_BYTES:
+                a = 2
+            else:
+                a = 0 if nbytes <= ONESHOT_MAX_BYTES else 1
+        if a == 0 and numel > self.lib.mpb_oneshot_max_elems(c_int(blocks or self._blocks(numel, 0))):
             a = 1
-        return a
+        if not blocks:
+            blocks = self._blocks(numel, a)
+        elif a != 0:
+            blocks = max(1, min(blocks, (numel // max(self.size, 1) + 2047) // 2048))
+        return a, int(blocks)
+
+    def _algo(self, algo: str, nbytes: int, numel: int) -> int:
+        return self._plan(algo, nbytes, numel)[0]
 
     def _blocks(self, numel: int, algo: int) -> int:
         per = 512 * 4
@@ -270,15 +322,37 @@ class PeerCollectives:
         # conservative: any bucket that may run two-shot keeps sliced optimizer state
         return self.size == 1
 
-    def _launch_ar(self, grads, params, shadows, m, v, hyper: Optional[Hyper], step: int, algo: str) -> None:
+    def _launch_ar(self, grads, params, shadows, m, v, hyper: Optional[Hyper], step: int, algo: str,
+                   wire: Optional[torch.Tensor] = None) -> None:
         n = grads.numel()
-        a = self._algo(algo, n * 4, n)
-        blocks = self._blocks(n, a)
-        g = self._peer_ptrs(grads)
+        a, blocks = self._plan(algo, n * (2 if wire is not None else 4), n)
         p = self._peer_ptrs(params)
         s = self._peer_ptrs(shadows)
         kind = 0 if hyper is None else (1 if hyper.kind == "adam" else 2)
         h = hyper or Hyper()
+        step_dev = c_void_p(0 if self.step_dev is None else self.step_dev.data_ptr())
+        stream = c_void_p(torch.cuda.current_stream().cuda_stream)
+        if wire is not None:
+            # bf16 wire: the kernel packs this rank's fp32 bucket into `wire`, peers read 2 bytes per element
+            if kind == 0:
+                raise ValueError("the bf16 wire format is only defined for the fused optimizer epilogue")
+            a = 2 if a == 2 else 1
+            mc_w = mc_p = mc_s = 0
+            if a == 2:
+                mc_w, mc_p, mc_s = self._mc_ptr(wire), self._mc_ptr(params), self._mc_ptr(shadows)
+                if mc_w == 0 or mc_p == 0 or (shadows is not None and mc_s == 0):
+                    a = 1
+            rc = self.lib.mpb_allreduce_fused_bf16wire(
+                c_void_p(grads.data_ptr()), self._peer_ptrs(wire), p, s, self._pads_arr,
+                c_void_p(self.epochs.data_ptr()), c_void_p(m.data_ptr()), c_void_p(0 if v is None else v.data_ptr()),
+                c_ll(n), c_int(self.rank), c_int(self.size), c_int(a), c_int(blocks), c_int(kind), c_int(step),
+                c_float(h.lr), c_float(h.beta1), c_float(h.beta2), c_float(h.eps), c_float(h.weight_decay),
+                c_float(h.momentum), step_dev, c_void_p(mc_w), c_void_p(mc_p), c_void_p(mc_s), stream)
+            self.launches += 1
+            if rc != 0:
+                raise RuntimeError("mpb_allreduce_fused_bf16wire failed: {}".format(rc))
+            return
+        g = self._peer_ptrs(grads)
         mc_g = mc_p = mc_s = 0
         if a == 2:
             mc_g, mc_p, mc_s = self._mc_ptr(grads), self._mc_ptr(params), self._mc_ptr(shadows)
@@ -289,9 +363,7 @@ class PeerCollectives:
             c_void_p(0 if m is None else m.data_ptr()), c_void_p(0 if v is None else v.data_ptr()),
             c_ll(n), c_int(self.rank), c_int(self.size), c_int(a), c_int(blocks), c_int(kind), c_int(step),
             c_float(h.lr), c_float(h.beta1), c_float(h.beta2), c_float(h.eps), c_float(h.weight_decay),
-            c_float(h.momentum), c_void_p(0 if self.step_dev is None else self.step_dev.data_ptr()),
-            c_void_p(mc_g), c_void_p(mc_p), c_void_p(mc_s),
-            c_void_p(torch.cuda.current_stream().cuda_stream))
+            c_float(h.momentum), step_dev, c_void_p(mc_g), c_void_p(mc_p), c_void_p(mc_s), stream)
         self.launches += 1
         if rc != 0:
             raise RuntimeError("mpb_allreduce_fused failed: {}".format(rc))
@@ -317,12 +389,12 @@ class PeerCollectives:
             raise RuntimeError("mpb_allreduce_bf16 failed: {}".format(rc))
 
     def all_reduce_update_(self, grads, params, state: Dict[str, torch.Tensor], shadow, hyper: Hyper, step: int,
-                           algo: str = "auto") -> None:
+                           algo: str = "auto", wire: Optional[torch.Tensor] = None) -> None:
         if hyper.kind == "adam":
             m, v = state["exp_avg"], state["exp_avg_sq"]
         else:
             m, v = state["momentum_buffer"], None
-        self._launch_ar(grads, params, shadow, m, v, hyper, step, algo)
+        self._launch_ar(grads, params, shadow, m, v, hyper, step, algo, wire)
 
     def broadcast_(self, view: torch.Tensor, root: int = 0) -> None:
         if self.size == 1:

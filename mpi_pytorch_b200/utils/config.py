@@ -51,6 +51,7 @@ class Settings:
     ALLREDUCE_ALGO: str = "auto"    # auto | oneshot | twoshot | nvls | nccl
     GRAD_DTYPE: str = "fp32"        # fp32 | bf16 wire/accumulate dtype of gradient buckets
     NATIVE_OPS: bool = True         # run the hand-written sm_100a kernels on CUDA
+    USE_CUDA_GRAPH: bool = True     # Trainer.fit replays the whole step as one CUDA graph for full batches
     SEED: int = 0
     TRAIN_CSV: str = "./data/train_sample.csv"
     TEST_CSV: str = "./data/test_sample.csv"

@@ -199,3 +199,57 @@ def test_mpi_tools_single_process_noop():
     assert mpi_tools.num_processes() == 1
     assert mpi_tools.mpi_avg_grads(m) is None and mpi_tools.sync_params(m) is None
     assert mpi_tools.mpi_sum(2.5, mpi_tools.SUM) == 2.5
+
+
+def test_bucket_schedule_ends_small():
+    """The last buckets to fire in backward cannot overlap with compute, so they are the small ones."""
+    m, _ = initialize_model("resnet34", 1000, False, use_pretrained=False)
+    lay = FlatLayout(list(m.parameters()), bucket_bytes=32 << 20, world=8)
+    mb = [b.numel * 4 / 2 ** 20 for b in lay.buckets]
+    assert mb[-1] <= 2.0 + 1e-6 and mb[-2] <= 8.0 + 1e-6 and max(mb) <= 32.0 + 1e-6
+    assert sum(len(b.params) for b in lay.buckets) == len(lay.params)
+    offs = sorted((s.offset, s.numel) for s in lay.slots.values())
+    for (o1, n1), (o2, _) in zip(offs, offs[1:]):
+        assert o1 + n1 <= o2
+    flat = FlatLayout(list(m.parameters()), bucket_bytes=32 << 20, world=8, tail_bytes=32 << 20)
+    assert len(flat.buckets) < len(lay.buckets)
+
+
+def _wire_worker(w, wire):
+    torch.manual_seed(0)
+    model = _tiny_nobn()
+    eng = FusedDataParallel(model, w, Hyper("adam", lr=1e-2), bucket_mb=0.001,
+                            grad_dtype=torch.bfloat16 if wire else torch.float32)
+    eng.sync_params(0)
+    g = torch.Generator().manual_seed(5)
+    X, Y = torch.randn(2, 8, 3, 8, 8, generator=g), torch.randint(0, 5, (2, 8), generator=g)
+    per = 8 // w.size
+    for s in range(2):
+        x, y = X[s, w.rank * per:(w.rank + 1) * per], Y[s, w.rank * per:(w.rank + 1) * per]
+        loss = nn.functional.cross_entropy(model(x), y)
+        eng.optimizer.zero_grad(); loss.backward(); eng.optimizer.step()
+    return [p.detach().clone() for p in model.parameters()], eng.wire_arena is not None
+
+
+def test_bf16_wire_format_in_the_engine_2_ranks():
+    """GRAD_DTYPE=bf16: gradients cross the wire as bf16 (one rounding per rank), sums and Adam stay fp32."""
+    a = run_ranks(_wire_worker, 2, (True,))
+    b = run_ranks(_wire_worker, 2, (False,))
+    assert a[0][1] and not b[0][1]
+    for x, y in zip(a[0][0], a[1][0]):
+        assert torch.equal(x, y)
+    for x, y in zip(a[0][0], b[0][0]):
+        assert torch.allclose(x, y, atol=2.5e-2)          # Adam's normalised step: bounded by ~2 * lr per step
+        assert not torch.equal(x, y) or x.numel() < 4
+
+
+def test_engine_suspended_keeps_gradients_local():
+    w = bootstrap.init_world("cpu")
+    torch.manual_seed(0)
+    model = _tiny_nobn()
+    eng = FusedDataParallel(model, w, Hyper("adam", lr=1e-2))
+    before = [p.detach().clone() for p in model.parameters()]
+    with eng.suspended():
+        nn.functional.cross_entropy(model(torch.randn(4, 3, 8, 8)), torch.randint(0, 5, (4,))).backward()
+    assert all(torch.equal(a, b) for a, b in zip(before, model.parameters()))
+    assert float(eng.grad_arena.abs().sum()) > 0 and eng.step_count == 0

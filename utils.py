@@ -46,6 +46,7 @@ BUCKET_MB = _S.BUCKET_MB
 ALLREDUCE_ALGO = _S.ALLREDUCE_ALGO
 GRAD_DTYPE = _S.GRAD_DTYPE
 NATIVE_OPS = _S.NATIVE_OPS
+USE_CUDA_GRAPH = _S.USE_CUDA_GRAPH
 SEED = _S.SEED
 TRAIN_CSV = _S.TRAIN_CSV
 TEST_CSV = _S.TEST_CSV
