@@ -24,11 +24,11 @@ def _trainer(model, hw, batch, dtype="bf16", lr=0.0, classes=24, **kw):
     return Trainer(s, w)
 
 
-def _grads(model, hw, batch, native):
+def _grads(model, hw, batch, native, dtype="bf16"):
     from mpi_pytorch_b200 import ops
     ops.set_native(native)
     try:
-        tr = _trainer(model, hw, batch)
+        tr = _trainer(model, hw, batch, dtype=dtype)
         for m in tr.model.modules():
             if isinstance(m, torch.nn.Dropout):
                 m.p = 0.0
@@ -42,54 +42,62 @@ def _grads(model, hw, batch, native):
                for n, p in tr.model.named_parameters() if p.requires_grad}
         fb = dict(ops.native().FALLBACKS) if native else {}
         tr.close()
-        return float(loss), out, fb
+        return float(loss.detach()), out, fb
     finally:
         ops.set_native(True)
+
+
+def _rel(a, ref):
+    return {n: float((a[n] - ref[n]).abs().max()) / (float(ref[n].abs().max()) + 1e-12) for n in ref}
 
 
 @pytest.mark.parametrize("name,hw", [("resnet18", 64), ("resnet34", 64), ("alexnet", 96), ("vgg", 64), ("vgg16", 64),
                                      ("squeezenet", 96), ("densenet", 64), ("inception", 128)])
 def test_zoo_gradients_match_torch_path(name, hw):
-    """Every parameter's gradient from the native kernels vs torch autograd over cuDNN/cuBLAS on the same bf16
-    inputs (was scripts/grad_check.py).  A wrong-but-finite gradient in any layer fails here."""
-    l1, g1, fb = _grads(name, hw, 8, True)
-    l0, g0, _ = _grads(name, hw, 8, False)
-    rel = {}
-    for n in g0:
-        denom = float(g0[n].abs().max()) + 1e-12
-        rel[n] = float((g1[n] - g0[n]).abs().max()) / denom
-    worst = sorted(rel.items(), key=lambda kv: -kv[1])
+    """Every parameter's gradient from the native bf16 kernels against an fp32 torch oracle (was
+    scripts/grad_check.py).  bf16 rounding noise is amplified by small-batch BatchNorm, so the yardstick is the error
+    torch's own bf16 path (autocast over cuDNN/cuBLAS) makes against the same oracle: a mis-indexed tap, a dropped
+    term or a wrong scale shows up as an error several times larger than that on the affected parameters."""
+    batch = 16
+    l32, g32, _ = _grads(name, hw, batch, False, "fp32")
+    lb, gb, _ = _grads(name, hw, batch, False, "bf16")
+    ln, gn, fb = _grads(name, hw, batch, True, "bf16")
+    e_n, e_b = _rel(gn, g32), _rel(gb, g32)
+    worst = sorted(((e_n[n], e_b[n], n) for n in e_n), reverse=True)
+    med = lambda d: sorted(d.values())[len(d) // 2]      # noqa: E731
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", "grad_check_{}.json".format(name)), "w") as fh:
-        json.dump({"model": name, "loss_native": l1, "loss_torch": l0, "fallbacks": fb, "worst": worst[:8],
-                   "n_params": len(rel), "median": sorted(rel.values())[len(rel) // 2]}, fh)
-    assert abs(l1 - l0) < 0.05 * max(1.0, abs(l0)), (l1, l0)
-    vals = sorted(rel.values())
-    # both sides compute in bf16, so they differ by rounding noise that grows with depth; a mis-indexed tap,
-    # a dropped term or a wrong scale shows up as rel ~ 1 on the affected parameters
-    assert vals[len(vals) // 2] < 0.06, ("median", vals[len(vals) // 2], worst[:4])
-    assert sum(1 for v in vals if v > 0.35) <= max(1, len(vals) // 50), worst[:6]
+        json.dump({"model": name, "loss_fp32": l32, "loss_torch_bf16": lb, "loss_native_bf16": ln, "fallbacks": fb,
+                   "worst_native_vs_fp32": worst[:8], "n_params": len(e_n), "median_native": med(e_n),
+                   "median_torch_bf16": med(e_b)}, fh)
+    assert abs(ln - l32) < 0.03 * max(1.0, abs(l32)), (ln, lb, l32)
+    assert med(e_n) <= 2.0 * med(e_b) + 0.02, (med(e_n), med(e_b), worst[:4])
+    bad = [(a, b, n) for a, b, n in worst if a > 4.0 * b + 0.15]
+    assert len(bad) <= max(1, len(e_n) // 50), bad[:6]
     assert fb == {}, fb
 
 
 def test_graph_replay_equals_eager_steps():
-    """Trainer.fit replays the captured step; three replays must leave the parameters where three eager steps do."""
+    """Trainer.fit replays the captured step; three replays must leave the parameters where three eager steps do.
+    SGD, so that rounding noise in a gradient stays proportional in the weights (Adam's g/sqrt(v) turns the noise of
+    near-zero gradients into full-size steps); the distance is judged against how far training moved the weights."""
     res = {}
     for graphed in (False, True):
-        tr = _trainer("resnet18", 64, 16, lr=1e-3, classes=16)
+        tr = _trainer("resnet18", 64, 16, lr=1e-2, classes=16, OPTIMIZER="sgd", MOMENTUM=0.9)
+        n = tr.engine.layout.total
+        p0 = tr.engine.param_arena[:n].clone()
         batches = list(tr.make_shard(total=48, shuffle=False))
         for x, y in batches:
             (tr.train_step_graphed if graphed else tr.train_step)(x, y)
         torch.cuda.synchronize()
-        res[graphed] = (tr.engine.param_arena[:tr.engine.layout.total].clone(), tr.engine.step_count,
-                        [b.clone() for b in tr.model.buffers()])
+        res[graphed] = (tr.engine.param_arena[:n].clone(), tr.engine.step_count,
+                        [b.clone() for b in tr.model.buffers()], p0)
         tr.close()
-    pa, pb = res[False][0], res[True][0]
+    pa, pb, p0 = res[False][0], res[True][0], res[False][3]
+    assert torch.equal(p0, res[True][3])
     assert res[False][1] == res[True][1] == 3
-    moved = float((pa - pa.mean()).abs().mean())
-    # split-K atomics order differs run to run, Adam's first steps move every weight by ~lr: compare to that scale
-    assert float((pa - pb).abs().max()) < 6.5e-3 and moved > 0
-    assert float((pa - pb).abs().mean()) < 3e-4
+    moved = float((pa - p0).norm())
+    assert moved > 0 and float((pa - pb).norm()) < 0.08 * moved, (float((pa - pb).norm()), moved)
     for a, b in zip(res[False][2], res[True][2]):
         assert torch.allclose(a.float(), b.float(), atol=2e-2, rtol=2e-2)
 
