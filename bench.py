@@ -161,7 +161,9 @@ def run_ddp(args) -> None:
     PyTorch user would write it for this box.  None of this repository's models, kernels or engine is on this path.
     Timed twice: eager launches, and the whole step (forward, backward, NCCL all-reduce, Adam) replayed as ONE CUDA
     graph -- ``value`` is the faster of the two, both are reported."""
-    os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")       # required for NCCL inside graph capture
+    # NCCL inside graph capture needs the watchdog's async error handling off; torchrun exports it as 1, so override
+    os.environ["TORCH_NCCL_ASYNC_ERROR_HANDLING"] = "0"
+    os.environ["NCCL_ASYNC_ERROR_HANDLING"] = "0"
     import torch
     import torch.distributed as dist
     import torchvision
@@ -256,9 +258,44 @@ def run_ddp(args) -> None:
             e2e_step(i)
         ms_e2e_eager, _ = timed(e2e_step, K)
     torch.cuda.current_stream(dev).wait_stream(side)
-    ms_graph = ms_e2e_graph = None
-    graph_err = None
+    res = {"ms_graph": None, "ms_e2e_graph": None, "graph_err": None, "loss": loss}
+
+    def emit():
+        clocks = sampler.stop() if sampler is not None else {}
+        if rank != 0:
+            return
+        ms_graph, ms_e2e_graph = res["ms_graph"], res["ms_e2e_graph"]
+        ms = min(m for m in (ms_eager, ms_graph) if m is not None)
+        ms_e2e = min(m for m in (ms_e2e_eager, ms_e2e_graph) if m is not None)
+        img = lambda m: None if m is None else B * world * K / (m / 1e3)      # noqa: E731
+        in_bytes = hx[0].numel() * hx[0].element_size() + hy[0].numel() * hy[0].element_size()
+        print(json.dumps({
+            "impl": "ddp", "metric": metric_name(args.model), "value": img(ms), "unit": "img/s", "n_gpus": world,
+            "steps": K, "warmup": max(W, 11), "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "gpu_launches": 0,
+            "e2e": {"value": img(ms_e2e), "unit": "img/s", "h2d_bytes_per_step": int(in_bytes), "d2h_bytes_per_step": 4,
+                    "ms_per_step": ms_e2e / K},
+            "config": {"model": args.model, "global_batch": B * world, "seq_len": args.image, "classes": args.classes,
+                       "parallelism": "dp{}".format(world), "optimizer": "adam(fused, capturable)",
+                       "stack": "torchvision.models.{} + torch DDP (NCCL) + cuDNN(benchmark) + channels_last + bf16 autocast"
+                                .format(ctor),
+                       "eager_img_s": img(ms_eager), "graphed_img_s": img(ms_graph),
+                       "eager_e2e_img_s": img(ms_e2e_eager), "graphed_e2e_img_s": img(ms_e2e_graph),
+                       "graph_error": res["graph_err"], "host_ms_per_eager_step": host_ms,
+                       "final_loss": float(res["loss"]) if res["graph_err"] is None else None,
+                       "l2": "per-step working set >> 126 MB L2; 4 input batches rotate; no explicit flush"},
+            "clocks": {k: clocks.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons")}}), flush=True)
+
     if os.environ.get("MPB_DDP_GRAPH", "1") != "0":
+        import signal
+
+        def on_alarm(_sig, _frm):          # a capture / replay that never returns: report the eager arm and leave
+            res["graph_err"] = "graph arm did not finish within {} s".format(limit)
+            emit()
+            os._exit(0)
+        limit = int(os.environ.get("MPB_DDP_GRAPH_TIMEOUT", "150"))
+        signal.signal(signal.SIGALRM, on_alarm)
+        signal.alarm(limit)
         try:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.stream(side):
@@ -280,33 +317,15 @@ def run_ddp(args) -> None:
                     return sloss
                 for i in range(3):
                     replay(i)
-                ms_graph, loss = timed(replay, K)
+                res["ms_graph"], res["loss"] = timed(replay, K)
                 for i in range(2):
                     replay_e2e(i)
-                ms_e2e_graph, _ = timed(replay_e2e, K)
+                res["ms_e2e_graph"], _ = timed(replay_e2e, K)
         except Exception as e:  # noqa: BLE001 - report the eager numbers and why the graph arm is missing
-            graph_err = repr(e)[:300]
-    clocks = sampler.stop() if sampler is not None else {}
-    if rank == 0:
-        ms = min(m for m in (ms_eager, ms_graph) if m is not None)
-        ms_e2e = min(m for m in (ms_e2e_eager, ms_e2e_graph) if m is not None)
-        img = lambda m: None if m is None else B * world * K / (m / 1e3)      # noqa: E731
-        in_bytes = hx[0].numel() * hx[0].element_size() + hy[0].numel() * hy[0].element_size()
-        print(json.dumps({
-            "impl": "ddp", "metric": metric_name(args.model), "value": img(ms), "unit": "img/s", "n_gpus": world,
-            "steps": K, "warmup": max(W, 11), "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "gpu_launches": 0,
-            "e2e": {"value": img(ms_e2e), "unit": "img/s", "h2d_bytes_per_step": int(in_bytes), "d2h_bytes_per_step": 4,
-                    "ms_per_step": ms_e2e / K},
-            "config": {"model": args.model, "global_batch": B * world, "seq_len": args.image, "classes": args.classes,
-                       "parallelism": "dp{}".format(world), "optimizer": "adam(fused, capturable)",
-                       "stack": "torchvision.models.{} + torch DDP (NCCL) + cuDNN(benchmark) + channels_last + bf16 autocast"
-                                .format(ctor),
-                       "eager_img_s": img(ms_eager), "graphed_img_s": img(ms_graph),
-                       "eager_e2e_img_s": img(ms_e2e_eager), "graphed_e2e_img_s": img(ms_e2e_graph),
-                       "graph_error": graph_err, "host_ms_per_eager_step": host_ms, "final_loss": float(loss),
-                       "l2": "per-step working set >> 126 MB L2; 4 input batches rotate; no explicit flush"},
-            "clocks": {k: clocks.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons")}}))
+            res["graph_err"] = repr(e)[:300]
+            res["ms_graph"] = res["ms_e2e_graph"] = None
+        signal.alarm(0)
+    emit()
     if world > 1:
         dist.destroy_process_group()
 
@@ -314,9 +333,9 @@ def run_ddp(args) -> None:
 # ------------------------------------------------------------------------------------------ our arm
 def dp_check(tr, batch) -> dict:
     """Driver-visible proof that the multi-GPU step is numerically the reference's (mpi_tools.py:30-37 then
-    main.py:155): from one saved state run the SAME batch twice -- (A) the product path, peer-memory kernels that
-    fuse sum, 1/W and Adam; (B) plain autograd, ``dist.all_reduce`` over NCCL, divide by W, the torch Adam formula --
-    and compare the resulting fp32 parameters."""
+    main.py:155): compute this rank's local gradients once, then from one saved state apply them twice -- (A) the
+    product path, peer-memory kernels that fuse sum, 1/W and Adam; (B) ``dist.all_reduce`` over NCCL, divide by W,
+    the torch Adam formula -- and compare the resulting fp32 parameters (expected: a few float ulps)."""
     import torch
     import torch.distributed as dist
     from mpi_pytorch_b200.ops import reference as ref
@@ -333,18 +352,21 @@ def dp_check(tr, batch) -> dict:
         eng.set_step(saved["step"])
         eng.refresh_shadow()
 
-    tr.train_step(*batch)                                          # (A)
+    with eng.suspended():                                          # local gradients of this rank's batch, ONCE
+        loss = tr.forward_loss(*batch)
+        eng.grad_arena.zero_()
+        loss.backward()
+    g_local = eng.grad_arena[:n].clone()
+    eng.reduce_and_step()                                          # (A) the product's kernels on those gradients
     torch.cuda.synchronize(tr.device)
     pa = eng.param_arena[:n].clone()
     shadow_ok = True
     if eng.shadow_arena is not None:
         shadow_ok = bool(torch.equal(eng.shadow_arena[:n], pa.to(eng.shadow_arena.dtype)))
     restore()
-    with eng.suspended():                                          # (B) hooks off: gradients stay local
-        loss = tr.forward_loss(*batch)
-        eng.grad_arena.zero_()
-        loss.backward()
-    g = eng.grad_arena[:n].clone()
+    g = g_local.clone()                                            # (B) NCCL + the torch formula on the SAME gradients
+    if eng.wire_arena is not None:
+        g = g.to(torch.bfloat16).float()                           # the bf16 wire rounds each rank's contribution once
     if W > 1:
         dist.all_reduce(g)
         g.div_(W)
@@ -364,8 +386,6 @@ def dp_check(tr, batch) -> dict:
         dist.all_gather(all_d, digest)
         same = all(int(d) == int(all_d[0]) for d in all_d)
     restore()
-    # an Adam step moves every weight by ~lr; split-K / atomics make the two gradient evaluations differ in the last
-    # bits, which Adam's g/sqrt(v) amplifies for near-zero gradients, so agreement is judged relative to the update
     return {"param_digest_equal_across_ranks": bool(same), "vs_nccl_max_abs": diff, "update_max_abs": upd,
             "bf16_shadow_exact": bool(shadow_ok)}
 

@@ -274,6 +274,17 @@ class FusedDataParallel:
         self._step_advanced = False
         self._reset_pending()
 
+    @torch.no_grad()
+    def reduce_and_step(self) -> None:
+        """Exchange + optimizer step over whatever the gradient arena holds NOW (every bucket, in schedule order).
+        With :meth:`suspended` this splits a step into "compute local gradients" and "reduce + update", which is
+        what lets a check feed the fused kernels and a plain all-reduce the very same gradients."""
+        if self.step_dev is not None and not self._step_advanced:
+            self.step_dev.add_(1)
+            self._step_advanced = True
+        self._reset_pending()
+        self.finish_step()
+
     def set_step(self, step: int) -> None:
         self.step_count = int(step)
         if self.step_dev is not None:
