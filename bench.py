@@ -69,6 +69,9 @@ def run_reference(args) -> None:
     mpi4py itself is not installable offline; baseline/mpi4py_shim provides MPI.COMM_WORLD over gloo."""
     ref_dir = os.path.join(ROOT, "baseline", "_ref")
     rank = int(os.environ.get("RANK", "0"))
+    if not os.path.exists(os.path.join(ref_dir, "mpi_tools.py")) and os.path.isdir("/root/reference") and rank == 0:
+        import subprocess                                # baseline/_ref is git-ignored: re-create it where the source exists
+        subprocess.run([sys.executable, os.path.join(ROOT, "baseline", "install_reference.py")], capture_output=True)
     if not os.path.exists(os.path.join(ref_dir, "mpi_tools.py")):
         if rank == 0:
             print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref missing (run baseline/install_reference.py)"}))
@@ -281,7 +284,8 @@ def run_ddp(args) -> None:
                                 .format(ctor),
                        "eager_img_s": img(ms_eager), "graphed_img_s": img(ms_graph),
                        "eager_e2e_img_s": img(ms_e2e_eager), "graphed_e2e_img_s": img(ms_e2e_graph),
-                       "graph_error": res["graph_err"], "host_ms_per_eager_step": host_ms,
+                       "graph_error": res["graph_err"], "graph_arm": res.get("graph_arm", "the eager step, captured"),
+                       "host_ms_per_eager_step": host_ms,
                        "final_loss": float(res["loss"]) if res["graph_err"] is None else None,
                        "l2": "per-step working set >> 126 MB L2; 4 input batches rotate; no explicit flush"},
             "clocks": {k: clocks.get(k) for k in ("sm_mhz", "sm_max_mhz", "reasons")}}), flush=True)
@@ -298,10 +302,39 @@ def run_ddp(args) -> None:
         signal.alarm(limit)
         try:
             graph = torch.cuda.CUDAGraph()
+            gstep = step
+            if world > 1:
+                # DDP's reducer is not capturable in this torch build (whole-step capture through the DDP wrapper
+                # never returned at N = 2).  The graphed arm therefore keeps model, optimizer, cuDNN kernels and NCCL
+                # but exchanges the gradients the plain way: every p.grad is a view of ONE flat buffer and a single
+                # ncclAllReduce(AVG) over it is captured right after backward (87 MB at ~700 GB/s is ~0.2 ms of a
+                # 24 ms step, so the lost overlap is far below the launch overhead the graph removes).
+                params = [p for p in net.parameters() if p.requires_grad]
+                flat = torch.zeros(sum(p.numel() for p in params), device=dev)
+                off = 0
+                for p in params:
+                    p.grad = flat[off:off + p.numel()].as_strided(p.shape, p.stride())
+                    off += p.numel()
+
+                def gstep(x, y):
+                    with torch.autocast("cuda", dtype=torch.bfloat16):
+                        out = net(x)
+                        if args.model == "inception":
+                            loss = crit(out[0].float(), y) + 0.4 * crit(out[1].float(), y)
+                        else:
+                            loss = crit(out.float(), y)
+                    flat.zero_()
+                    loss.backward()
+                    dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+                    opt.step()
+                    return loss.detach()
+                res["graph_arm"] = "plain module + one flat NCCL all-reduce(AVG) + fused Adam, whole step in one CUDA graph"
             with torch.cuda.stream(side):
+                for i in range(3):
+                    gstep(xs[i % 4], ys[i % 4])
                 sync_all()
                 with torch.cuda.graph(graph, stream=side):
-                    sloss = step(sx, sy)
+                    sloss = gstep(sx, sy)
 
                 def replay(i):
                     sx.copy_(xs[i % 4], non_blocking=True)
@@ -670,10 +703,7 @@ def run_pipeline(args) -> None:
         if cuda:
             m = m.to(memory_format=torch.channels_last).to(torch.bfloat16)
         return m
-    coll = None
-    if cuda and world.size > 1:
-        from mpi_pytorch_b200.parallel.collectives import make_collectives
-        coll = make_collectives(world, "auto")
+    coll = tr.engine.coll if (cuda and world.size > 1) else None      # the trainer's peer-memory runtime, reused
     pipe = EvalPipeline(world, n, raw_hw, out_hw, frames, labels, model_fn, micro_batch=mb, seed=0, dtype=dtype,
                         collectives=coll)
     acc = pipe.run()

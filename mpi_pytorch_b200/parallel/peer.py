@@ -76,15 +76,24 @@ class _FdRelay:
     Rank 0 listens on an abstract AF_UNIX socket; every other rank keeps one connection to it.  An exchange
     sends each rank's descriptor to rank 0 (SCM_RIGHTS), which then hands every rank the full list."""
 
+    _seq = 0                  # several relays may live in one process (trainer, then the eval pipeline's collectives)
+
     def __init__(self, world):
         self.rank, self.size = world.rank, world.size
         name = [None]
+        _FdRelay._seq += 1
         if self.rank == 0:
-            name[0] = "\0mpb-fd-{}-{}".format(os.getpid(), os.environ.get("MASTER_PORT", "0"))
-            self.srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
-            self.srv.bind(name[0])
-            self.srv.listen(self.size)
+            try:
+                cand = "\0mpb-fd-{}-{}-{}".format(os.getpid(), os.environ.get("MASTER_PORT", "0"), _FdRelay._seq)
+                self.srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                self.srv.bind(cand)
+                self.srv.listen(self.size)
+                name[0] = cand
+            except OSError:
+                name[0] = None            # every rank learns of the failure below: nobody is left waiting
         dist.broadcast_object_list(name, src=0)
+        if name[0] is None:
+            raise OSError("fd relay: rank 0 could not open its listening socket")
         self.conns: Dict[int, socket.socket] = {}
         if self.rank == 0:
             for _ in range(self.size - 1):
