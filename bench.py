@@ -360,6 +360,11 @@ def run_ddp(args) -> None:
         signal.alarm(0)
     emit()
     if world > 1:
+        # tearing the NCCL communicator down after it took part in a graph capture never returned here (N = 2):
+        # the result is printed, every rank leaves without the collective destroy
+        sys.stdout.flush()
+        os._exit(0)
+    if world > 1:
         dist.destroy_process_group()
 
 
@@ -655,12 +660,11 @@ def run_pipeline(args) -> None:
     B = 128 if cuda else 16
     dtype = torch.bfloat16 if cuda else torch.float32
 
-    def frames(i0: int, i1: int) -> torch.Tensor:
+    def make_frames(i0: int, i1: int, device) -> torch.Tensor:
         """Learnable stand-in for Herbarium JPEGs: noise plus a class-dependent colour cast (uint8 HWC)."""
-        idx = torch.arange(i0, i1)
-        lab = labels[idx]
-        g = torch.Generator().manual_seed(7919 + i0)
-        x = torch.randint(0, 96, (i1 - i0, raw_hw[0], raw_hw[1], 3), generator=g, dtype=torch.int32)
+        lab = labels[i0:i1].to(device)
+        g = torch.Generator(device=device).manual_seed(7919 + i0)
+        x = torch.randint(0, 96, (i1 - i0, raw_hw[0], raw_hw[1], 3), generator=g, dtype=torch.int32, device=device)
         for c in range(3):
             x[:, :, :, c] += ((lab % 3 == c).int() * (40 + 8 * (lab % 16).int())).view(-1, 1, 1)
             x[:, : raw_hw[0] // 2, :, c] += (((lab // 3) % 3 == c).int() * (6 * (lab % 24).int())).view(-1, 1, 1)
@@ -668,6 +672,19 @@ def run_pipeline(args) -> None:
 
     from mpi_pytorch_b200.data.synthetic import synth_labels
     labels = synth_labels(0, torch.arange(n), classes)
+    # The whole "decoded" test set is generated once, up front, on every rank's device (same seeds -> same frames);
+    # the reader rank additionally keeps it in pinned host memory, which is what its `source` reads from, so every
+    # message of the timed pipeline still starts with a host -> device copy of raw frames.
+    CH = 500
+    dev_frames = torch.cat([make_frames(i, min(i + CH, n), dev) for i in range(0, n, CH)])
+    host_frames = None
+    if world.rank == 0:
+        host_frames = dev_frames.cpu()
+        if cuda:
+            host_frames = host_frames.pin_memory()
+
+    def frames(i0: int, i1: int) -> torch.Tensor:
+        return host_frames[i0:i1]
     s = Settings(MODEL_NAME="resnet18", NUM_CLASSES=classes, BATCH_SIZE=B, HEIGHT=out_hw[0], WIDTH=out_hw[1],
                  USE_PRETRAINED=False, DTYPE="bf16", LR=1e-3, SEED=0, VALIDATE=False)
     tr = Trainer(s, world)
@@ -679,9 +696,7 @@ def run_pipeline(args) -> None:
     last = None
     for step in range(train_steps):
         i0 = int(torch.randint(0, n - B + 1, (1,), generator=g))         # a window of B consecutive samples
-        raw = frames(i0, i0 + B)
-        if cuda:
-            raw = raw.pin_memory().to(dev, non_blocking=True)
+        raw = dev_frames[i0:i0 + B]
         x = ops.normalize_u8(ops.resize_u8(raw, out_hw[0], out_hw[1], "bicubic"), dtype)
         if cuda:
             x = x.contiguous(memory_format=torch.channels_last)
@@ -701,7 +716,7 @@ def run_pipeline(args) -> None:
         m, _ = initialize_model("resnet18", classes, feature_extract=False, use_pretrained=False)
         m.load_state_dict(torch.load(checkpoint_path(ckdir, "resnet18"), map_location="cpu", weights_only=False)["state_dict"])
         if cuda:
-            m = m.to(memory_format=torch.channels_last).to(torch.bfloat16)
+            m = ops.prepare_inference(m.to(dev).to(memory_format=torch.channels_last), torch.bfloat16)
         return m
     coll = tr.engine.coll if (cuda and world.size > 1) else None      # the trainer's peer-memory runtime, reused
     pipe = EvalPipeline(world, n, raw_hw, out_hw, frames, labels, model_fn, micro_batch=mb, seed=0, dtype=dtype,
@@ -722,7 +737,7 @@ def run_pipeline(args) -> None:
         with torch.no_grad():
             for i0 in range(0, n, mb):
                 i1 = min(i0 + mb, n)
-                x = ops.normalize_u8(ops.resize_u8(frames(i0, i1).to(dev), out_hw[0], out_hw[1], "bicubic"), dtype)
+                x = ops.normalize_u8(ops.resize_u8(dev_frames[i0:i1], out_hw[0], out_hw[1], "bicubic"), dtype)
                 if cuda:
                     x = x.contiguous(memory_format=torch.channels_last)
                 correct += ops.count_correct(m(x), labels[i0:i1].to(dev))

@@ -66,9 +66,10 @@ def pipeline(world=None, settings=None, n_samples=None):
         else:
             logger.warning('no checkpoint at {}: predicting with random weights'.format(path))
         if world.device.type == 'cuda':
-            model = model.to(memory_format=torch.channels_last)
-            if settings.DTYPE == 'bf16':
-                model = model.to(torch.bfloat16)
+            from mpi_pytorch_b200 import ops
+            model = model.to(world.device).to(memory_format=torch.channels_last)
+            # parameters and BatchNorm statistics stay fp32; GEMM-shaped weights get a bf16 compute copy
+            model = ops.prepare_inference(model, torch.bfloat16 if settings.DTYPE == 'bf16' else torch.float32)
         return model
     dtype = torch.bfloat16 if (world.device.type == 'cuda' and settings.DTYPE == 'bf16') else torch.float32
     coll = None

@@ -139,3 +139,11 @@ def cat_channels(tensors):
     if _nat(tensors[0]):
         return native().cat_channels(tensors)
     return torch.cat(tensors, dim=1)
+
+
+def prepare_inference(model, dtype=torch.bfloat16):
+    """Forward-only preparation of a model outside the DP engine (bf16 compute copies of the GEMM-shaped weights on
+    CUDA; a no-op besides ``eval()`` on the torch path)."""
+    if _STATE["enabled"] and any(p.is_cuda for p in model.parameters()):
+        return native().prepare_inference(model, dtype)
+    return model.eval()

@@ -93,6 +93,29 @@ def _pair(v) -> Tuple[int, int]:
     return (int(v[0]), int(v[1])) if isinstance(v, (tuple, list)) else (int(v), int(v))
 
 
+def _f32(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """Bias / affine vectors are read by the kernels as fp32: cast the rare all-bf16 module instead of misreading it."""
+    if t is None:
+        return None
+    t = t.detach()
+    return t if t.dtype == torch.float32 else t.float()
+
+
+def prepare_inference(model: torch.nn.Module, dtype: torch.dtype = torch.bfloat16) -> torch.nn.Module:
+    """Make a model ready for forward-only use on the native path WITHOUT the DP engine: parameters, BatchNorm
+    statistics and biases stay fp32 (what the kernels read), and every GEMM-shaped weight gets the bf16 compute copy
+    the engine would otherwise maintain, so no per-call cast happens (eval pipeline predictors,
+    /root/reference/evaluation_pipeline.py:138-147)."""
+    with torch.no_grad():
+        for p in model.parameters():
+            if p.dim() >= 2 and p.dtype == torch.float32 and dtype != torch.float32:
+                if p.dim() == 4:
+                    p._mpb_shadow = p.detach().to(dtype).contiguous(memory_format=torch.channels_last)
+                else:
+                    p._mpb_shadow = p.detach().to(dtype).contiguous()
+    return model.eval()
+
+
 def _compute_weight(w: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
     sh = getattr(w, "_mpb_shadow", None)
     if sh is not None and sh.dtype == dtype:
@@ -122,15 +145,15 @@ class _ConvFn(torch.autograd.Function):
         ctx.xcol = None
         ctx.xs2d = None
         if tc.stem_s2d_ok(x, w, stride, padding, dilation, groups):
-            y, stats, ctx.xs2d = tc.conv_fprop_stem(x, w, None if bias is None else bias.detach(), padding, want_stats)
+            y, stats, ctx.xs2d = tc.conv_fprop_stem(x, w, _f32(bias), padding, want_stats)
         elif tc.fprop_ok(x, w, stride, padding, dilation, groups):
-            y, stats = tc.conv_fprop(x, w, None if bias is None else bias.detach(), stride, padding, want_stats)
+            y, stats = tc.conv_fprop(x, w, _f32(bias), stride, padding, want_stats)
         elif tc.im2col_ok(x, w, stride, padding, dilation, groups):
-            y, stats, ctx.xcol = tc.conv_fprop_im2col(x, w, None if bias is None else bias.detach(), stride, padding,
+            y, stats, ctx.xcol = tc.conv_fprop_im2col(x, w, _f32(bias), stride, padding,
                                                       want_stats)
         else:
             _note_fallback("conv_fprop")
-            b = None if bias is None else bias.detach().to(x.dtype)
+            b = _f32(bias).to(x.dtype)
             y = _nhwc(F.conv2d(x, w, b, stride, padding, dilation, groups))
             if want_stats:
                 stats = bn_stats(y)
@@ -204,9 +227,9 @@ class _LinearFn(torch.autograd.Function):
         ctx.conf = (bias is not None, weight.dtype)
         tc = _gemm()
         if tc.gemm_supported(x, w):
-            return tc.linear_fwd(x, w, None if bias is None else bias.detach())
+            return tc.linear_fwd(x, w, _f32(bias))
         _note_fallback("linear_fwd")
-        return F.linear(x, w, None if bias is None else bias.detach().to(x.dtype))
+        return F.linear(x, w, _f32(bias).to(x.dtype))
 
     @staticmethod
     def backward(ctx, gy):
@@ -319,7 +342,8 @@ def bn_stats(y: torch.Tensor) -> torch.Tensor:
 def _bn_ok(x, bn) -> bool:
     c = x.shape[1]
     return (x.dim() == 4 and c % 8 == 0 and c <= 2048 and x.dtype in (torch.bfloat16, torch.float32)
-            and bn.affine and bn.track_running_stats)
+            and bn.affine and bn.track_running_stats and bn.weight.dtype == torch.float32
+            and bn.running_mean.dtype == torch.float32)
 
 
 def batch_norm_act(x, bn, residual=None, relu=False, sums=None):

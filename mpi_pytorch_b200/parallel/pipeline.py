@@ -222,20 +222,29 @@ class EvalPipeline:
 
     # ------------------------------------------------------------------ stage 0: read + dispatch (C19)
     def _run_reader(self) -> None:
-        copy_stream = torch.cuda.Stream(self.dev) if self.cuda else None
-        staged: List[Optional[Tuple[torch.Tensor, torch.Tensor]]] = [None, None]
+        pin = (lambda t: t.pin_memory()) if self.cuda else (lambda t: t)
+        raw_stage = [pin(torch.zeros(self.raw_shape, dtype=torch.uint8)) for _ in range(2)]
+        hdr_stage = [pin(torch.zeros(self.mb + HDR_ROWS_EXTRA, HDR_COLS, dtype=torch.int64)) for _ in range(2)]
+        staged: List[Optional[Tuple[torch.Tensor, torch.Tensor, int]]] = [None, None]
 
-        def stage_host(idx: int) -> Tuple[torch.Tensor, torch.Tensor]:
-            """Host side of one message: frames padded into the fixed canvas + the header rows, in pinned memory."""
+        def stage_host(idx: int) -> Tuple[torch.Tensor, torch.Tensor, int]:
+            """Host side of one message: the frames (padded into the fixed canvas when they are smaller) and the
+            header rows, in pinned memory.  Frames that already fill the canvas are sent from where the source keeps
+            them, without a staging copy."""
             i0, i1 = self._ids(idx)
             k = i1 - i0
             frames = self.source(i0, i1)
-            raw = torch.zeros(self.raw_shape, dtype=torch.uint8)
-            hdr = torch.zeros(self.mb + HDR_ROWS_EXTRA, HDR_COLS, dtype=torch.int64)
+            raw, hdr = raw_stage[idx % 2], hdr_stage[idx % 2]
+            hdr.zero_()
             if torch.is_tensor(frames):
-                raw[:k, :frames.shape[1], :frames.shape[2]] = frames
                 hdr[1:k + 1, 3], hdr[1:k + 1, 4] = frames.shape[1], frames.shape[2]
+                if tuple(frames.shape[1:]) == tuple(self.raw_shape[1:]) and frames.is_contiguous():
+                    raw = frames                              # k rows; the rest of the device buffer is don't-care
+                else:
+                    raw.zero_()
+                    raw[:k, :frames.shape[1], :frames.shape[2]] = frames
             else:
+                raw.zero_()
                 for j, f in enumerate(frames):
                     raw[j, :f.shape[0], :f.shape[1]] = f
                     hdr[1 + j, 3], hdr[1 + j, 4] = f.shape[0], f.shape[1]
@@ -243,15 +252,18 @@ class EvalPipeline:
             hdr[1:k + 1, 0] = self.labels[i0:i1]
             hdr[1:k + 1, 1] = self.assign[i0:i1]
             hdr[1:k + 1, 2] = torch.arange(i0, i1)
-            if self.cuda:
-                raw, hdr = raw.pin_memory(), hdr.pin_memory()
-            return raw, hdr
+            return raw, hdr, k
+
+        done: List[Optional[object]] = [None, None]          # event: the H2D copies out of staging slot s finished
 
         def body(idx: int) -> None:
-            raw, hdr = staged[idx % 2]
+            raw, hdr, k = staged[idx % 2]
             m = self._out_msg(self.roles.resizer, "resize", self.raw_shape, torch.uint8)
-            m.payload.copy_(raw, non_blocking=True)
+            m.payload[:raw.shape[0]].copy_(raw, non_blocking=True)
             m.header.copy_(hdr, non_blocking=True)
+            if self.cuda:
+                done[idx % 2] = torch.cuda.Event()
+                done[idx % 2].record()
             self._emit(self.roles.resizer, "resize", m, idx)
 
         if self.n_front:
@@ -259,8 +271,9 @@ class EvalPipeline:
         for idx in range(self.n_front):
             self._timed(body, idx)
             if idx + 1 < self.n_front:
-                staged[(idx + 1) % 2] = stage_host(idx + 1)        # decode of i+1 overlaps the transfer of i
-        del copy_stream
+                if done[(idx + 1) % 2] is not None:
+                    done[(idx + 1) % 2].synchronize()           # staging slot free again (copy of message idx-1 done)
+                staged[(idx + 1) % 2] = stage_host(idx + 1)     # decode of i+1 overlaps the transfer of i
 
     # ------------------------------------------------------------------ stage 1: resize (C20)
     def _stage_resize(self, m: _Msg, idx: int) -> None:

@@ -10,7 +10,7 @@ run() {  # name timeout cmd...
   PORT=$((PORT+1))
   local TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT"
   local t0=$(date +%s)
-  timeout -k 10 $t $TR "$@" > $OUT/$name.json 2> $OUT/$name.err
+  timeout -k 10 ${MPB_SUITE_TIMEOUT:-$t} $TR "$@" > $OUT/$name.json 2> $OUT/$name.err
   echo "== $name rc=$? $(( $(date +%s) - t0 ))s"; tail -n 1 $OUT/$name.json | cut -c1-300
 }
 K=${MPB_SUITE_STEPS:-10}; W=${MPB_SUITE_WARMUP:-3}
