@@ -146,8 +146,9 @@ class EvalPipeline:
                  source: Callable[[int, int], Union[torch.Tensor, List[torch.Tensor]]], labels: torch.Tensor,
                  model_fn: Callable[[], torch.nn.Module], micro_batch: int = 32, seed: int = 0,
                  dtype: torch.dtype = torch.float32, resize_mode: str = "bicubic", collectives=None,
-                 frame_hw: Optional[torch.Tensor] = None):
+                 frame_hw: Optional[torch.Tensor] = None, use_graph: bool = True):
         self.w = world
+        self.use_graph = use_graph
         self.coll = collectives        # optional: sums the per-rank counts with the peer-memory count kernel (K13)
         self.dev = world.device
         self.cuda = self.dev.type == "cuda"
@@ -364,18 +365,52 @@ class EvalPipeline:
         self._emit(p, "predict", out, sent)
 
     # ------------------------------------------------------------------ stage 3: predict (C22)
+    def _prepare_predict_graph(self) -> None:
+        """Capture ``model(x) -> count_correct`` for a full micro-batch once, before any p2p traffic is posted: a
+        predictor's per-message work then is two device copies and one graph replay instead of ~100 eager launches
+        (the eager forward of ResNet-18 at batch 64 is host-bound: ~2 ms of launches for ~0.3 ms of kernels)."""
+        self._pgraph = None
+        if not (self.cuda and self.use_graph):
+            return
+        self._px = torch.zeros(self.batch_shape, dtype=self.dtype, device=self.dev).contiguous(
+            memory_format=torch.channels_last)
+        self._plab = torch.zeros(self.mb, dtype=torch.int64, device=self.dev)
+        self._pcount = torch.zeros((), dtype=torch.int64, device=self.dev)
+        cur = torch.cuda.current_stream(self.dev)
+        side = torch.cuda.Stream(self.dev)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(2):
+                ops.count_correct(self._model(self._px), self._plab)
+        cur.wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g), torch.no_grad():
+                self._pcount.copy_(ops.count_correct(self._model(self._px), self._plab))
+            self._pgraph = g
+        except Exception as e:  # noqa: BLE001 - fall back to eager launches, say so once
+            self.log.warning("predictor graph capture failed, running eagerly: {!r}".format(e))
+            self._pgraph = None
+
     def _stage_predict(self, m: _Msg, idx: int) -> None:
         if self._model is None:
             self._model = self.model_fn().to(self.dev).eval()
         me = self.w.rank
         mine = int((self.assign == me).sum())
         k = min(self.mb, mine - idx * self.mb)                        # this message's image count, known a priori
-        with torch.no_grad():
-            x = m.payload[:k]
-            if self.cuda:
-                x = x.contiguous(memory_format=torch.channels_last)
-            out = self._model(x)
-        self.correct += ops.count_correct(out, m.header[1:k + 1, 0].contiguous())
+        if getattr(self, "_pgraph", None) is not None and k == self.mb:
+            self._px.copy_(m.payload)
+            self._plab.copy_(m.header[1:, 0])
+            self._pgraph.replay()
+            self.correct += self._pcount
+        else:
+            with torch.no_grad():
+                x = m.payload[:k]
+                if self.cuda:
+                    x = x.contiguous(memory_format=torch.channels_last)
+                out = self._model(x)
+            self.correct += ops.count_correct(out, m.header[1:k + 1, 0].contiguous())
         # protocol self-check, accumulated on the device and read once at the end
         want_last = int(idx == self.n_pred[me] - 1)
         bad = (m.header[0, 0] != k).to(torch.int64) + (m.header[0, 1] != want_last).to(torch.int64) + \
@@ -398,6 +433,8 @@ class EvalPipeline:
         r, roles = self.w.rank, self.roles
         if r in roles.predictors and self._model is None:
             self._model = self.model_fn().to(self.dev).eval()
+        if r in roles.predictors:
+            self._prepare_predict_graph()
         if self.w.size > 1:
             dist.barrier()
         ev0 = ev1 = None

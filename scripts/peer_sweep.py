@@ -99,7 +99,9 @@ def main():
     # leaves more SMs to the backward kernels the collective overlaps with
     table = []
     for mb in sizes_mb:
-        cand = [r for r in rows if r["MB"] == mb and r["algo"] != "nccl"]
+        # grids above 64 CTAs are measured but not chosen: a comm CTA (512 threads, ~116 registers) owns its SM, and
+        # the collective shares the GPU with the backward kernels it overlaps
+        cand = [r for r in rows if r["MB"] == mb and r["algo"] != "nccl" and r["grid"] <= 64]
         best = min(c["adam_us"] for c in cand)
         pick = min((c for c in cand if c["adam_us"] <= best * 1.03), key=lambda c: c["grid"])
         table.append([int(mb * 2 ** 20), pick["algo"], pick["grid"]])
