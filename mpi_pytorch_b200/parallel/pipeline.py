@@ -188,6 +188,21 @@ class EvalPipeline:
             if a != b and (a, b) not in self._groups and self.w.size > 1:
                 self._groups[(a, b)] = dist.new_group([a, b])
 
+    def _warm_edges(self) -> None:
+        """One throw-away message over every edge before the timed region: NCCL builds a p2p connection lazily on
+        the first send/recv of a communicator (tens to hundreds of ms per edge, and the edges form a chain)."""
+        if self.w.size == 1:
+            return
+        r = self.w.rank
+        buf = torch.zeros(1 << 20, dtype=torch.uint8, device=self.dev)
+        for (a, b), grp in self._groups.items():
+            if r == a:
+                dist.send(buf, dst=b, group=grp)
+            elif r == b:
+                dist.recv(buf, src=a, group=grp)
+        if self.cuda:
+            torch.cuda.synchronize(self.dev)
+
     def _out_msg(self, dest: int, stage: str, shape, dtype) -> _Msg:
         if dest == self.w.rank:
             if stage not in self._local:
@@ -435,6 +450,7 @@ class EvalPipeline:
             self._model = self.model_fn().to(self.dev).eval()
         if r in roles.predictors:
             self._prepare_predict_graph()
+        self._warm_edges()
         if self.w.size > 1:
             dist.barrier()
         ev0 = ev1 = None
