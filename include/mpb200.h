@@ -85,6 +85,10 @@ int mpb_dropout(const void* x, void* y, long long n, unsigned int seed, float p,
  * (torch.cat of the DenseNet / Inception / Fire blocks, models.py:56-87).                                       */
 int mpb_copy_rows(const void* src, long long src_pitch, void* dst, long long dst_pitch, long long M, long long row_bytes,
                   void* stream);
+/* dst[r][j] (+)= src[r][idx[j]] (idx[j] < 0 -> 0): the stem filter's relayout between KRSC and the space-to-depth
+ * form of the tensor-core stem kernels (torchvision stems reached from models.py:33,41,77).  dtype 0 fp32, 1 bf16. */
+int mpb_gather_cols(const void* src, const long long* idx, void* dst, int rows, int src_cols, int dst_cols,
+                    int src_dtype, int dst_dtype, int accumulate, void* stream);
 /* `epoch` (nullable device pointer): a step counter mixed into the seed on the device, so a captured launch draws a
  * new mask on every CUDA-graph replay; the backward call of the same step passes the same pointer and seed.      */
 int mpb_dropout_ex(const void* x, void* y, long long n, unsigned int seed, const long long* epoch, float p, int dtype,

@@ -675,3 +675,41 @@ MPB_API int mpb_copy_rows(const void* src, long long src_pitch, void* dst, long 
   MPB_CHECK_LAUNCH();
   return 0;
 }
+
+
+// Column gather of a small row-major matrix: dst[r][j] (+)= src[r][idx[j]] for idx[j] >= 0, else 0.  Used to move
+// the 7x7x3 stem filter between its KRSC layout and the space-to-depth layout the tensor-core stem kernels read
+// (forward: bf16 compute copy -> [K][4 taps][64]; backward: fp32 [K][256] filter gradient -> += the parameter's
+// slot of the gradient arena), replacing torch.cat + advanced indexing (+ a zeros fill and an add on the way back).
+namespace {
+template <typename TI, typename TO>
+__global__ void gather_cols_kernel(const TI* __restrict__ src, const long long* __restrict__ idx, TO* __restrict__ dst,
+                                   int rows, int src_cols, int dst_cols, int accumulate) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= (long long)rows * dst_cols) return;
+  const int r = (int)(i / dst_cols), j = (int)(i % dst_cols);
+  const long long k = idx[j];
+  float v = (k >= 0 && k < src_cols) ? to_f(src[(long long)r * src_cols + k]) : 0.f;
+  if (accumulate) v += to_f(dst[i]);
+  dst[i] = from_f<TO>(v);
+}
+}  // namespace
+
+// dtype codes: 0 = fp32, 1 = bf16 (as everywhere in this library)
+MPB_API int mpb_gather_cols(const void* src, const long long* idx, void* dst, int rows, int src_cols, int dst_cols,
+                            int src_dtype, int dst_dtype, int accumulate, void* stream) {
+  if (rows <= 0 || dst_cols <= 0) return 0;
+  const long long n = (long long)rows * dst_cols;
+  const int blocks = (int)((n + 255) / 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (src_dtype == 1 && dst_dtype == 1)
+    gather_cols_kernel<__nv_bfloat16, __nv_bfloat16><<<blocks, 256, 0, st>>>((const __nv_bfloat16*)src, idx, (__nv_bfloat16*)dst, rows, src_cols, dst_cols, accumulate);
+  else if (src_dtype == 0 && dst_dtype == 1)
+    gather_cols_kernel<float, __nv_bfloat16><<<blocks, 256, 0, st>>>((const float*)src, idx, (__nv_bfloat16*)dst, rows, src_cols, dst_cols, accumulate);
+  else if (src_dtype == 0 && dst_dtype == 0)
+    gather_cols_kernel<float, float><<<blocks, 256, 0, st>>>((const float*)src, idx, (float*)dst, rows, src_cols, dst_cols, accumulate);
+  else
+    return -1;
+  MPB_CHECK_LAUNCH();
+  return 0;
+}

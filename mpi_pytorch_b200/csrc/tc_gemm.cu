@@ -57,19 +57,23 @@ struct TcParams {
   int stages;               // smem ring depth (fewer stages -> more co-resident CTAs per SM)
   // strided dgrad, one launch per output parity class (ph, pw): valid filter taps r = r0 + st*i, s = s0 + st*j
   int st, ph, pw, r0, s0, nr, ns, lower_h, lower_w, Hfull, Wfull;
-  int a_shift;              // experiment: A stage holds rows [m0 - a_shift, ...); the UMMA descriptor starts a_shift rows in
+  int nclass;               // strided dgrad as ONE launch: blockIdx.z = output parity class, geometry in cls[z]
+  struct StridedClass { int M, Hout, Wout, num_kb, ph, pw, r0, s0, nr, ns, lower_h, lower_w; } cls[4];
   int cluster;              // 1, or 2: CTA pair (cta_group::2) computes a 256 x BN tile; each CTA stages its 128 A rows and HALF of B
 };
+
+struct ExtraMaps { CUtensorMap m[3]; };   // im2col maps of parity classes 1..3 (class 0 uses tmA)
 
 // kTwo = CTA-pair (cta_group::2) build.  It is a separate instantiation because a kernel that contains
 // cta_group::2 instructions can only be launched with an even cluster size (plain launches fail with error 912).
 template <bool kTwo>
 __global__ void __launch_bounds__(kThreads, 4)
-tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ ExtraMaps tmX, const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // carve: [stages][A 16KB][B BN*128B] | barriers
   const int b_stage_bytes = (p.BN / p.cluster) * BK * 2;   // a CTA pair splits the B tile between its two shared memories
-  const int a_bytes = A_STAGE_BYTES + (p.a_shift ? 2048 : 0);   // shifted-view experiment: 16 extra rows
+  constexpr int a_bytes = A_STAGE_BYTES;
   const int stage_bytes = a_bytes + b_stage_bytes;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   __shared__ uint64_t full_bar[8], empty_bar[8], tmem_full_bar;
@@ -86,14 +90,28 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     cblk_fixed = blockIdx.y % p.tap_cols;
     n0 = 0;
   }
-  const int kb_begin = blockIdx.z * p.kb_per_split;
-  const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+  // geometry: the launch's own, or (single-launch strided dgrad) that of the parity class this CTA works on
+  const bool multi = p.mode == MODE_DGRAD_STRIDED && p.nclass > 1;
+  const int cz = multi ? (int)blockIdx.z : 0;
+  const CUtensorMap* mapA = (multi && cz > 0) ? &tmX.m[cz - 1] : &tmA;
+  int gM = p.M, gH = p.Hout, gW = p.Wout, g_ph = p.ph, g_pw = p.pw, g_r0 = p.r0, g_s0 = p.s0, g_nr = p.nr, g_ns = p.ns;
+  int g_lower_h = p.lower_h, g_lower_w = p.lower_w, g_num_kb = p.num_kb, g_kbps = p.kb_per_split;
+  if (multi) {
+    const TcParams::StridedClass& c = p.cls[cz];
+    gM = c.M; gH = c.Hout; gW = c.Wout; g_ph = c.ph; g_pw = c.pw; g_r0 = c.r0; g_s0 = c.s0; g_nr = c.nr; g_ns = c.ns;
+    g_lower_h = c.lower_h; g_lower_w = c.lower_w; g_num_kb = c.num_kb; g_kbps = c.num_kb;
+    // a class with fewer rows than the grid covers: the whole CTA (pair) leaves before touching barriers or TMEM
+    const int lead_m0 = (kTwo ? (int)(blockIdx.x & ~1u) : (int)blockIdx.x) * BM;
+    if (lead_m0 >= gM) return;
+  }
+  const int kb_begin = multi ? 0 : blockIdx.z * g_kbps;
+  const int kb_end = min(g_num_kb, kb_begin + g_kbps);
   const int nkb = kb_end - kb_begin;
   uint32_t tmem_cols = 32;
   while ((int)tmem_cols < p.BN) tmem_cols <<= 1;
 
   if (threadIdx.x == 0) {
-    prefetch_tmap(&tmA);
+    prefetch_tmap(mapA);
     prefetch_tmap(&tmB);
     for (int i = 0; i < stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     mbar_init(&tmem_full_bar, 1);
@@ -117,10 +135,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // pixel decomposition of the tile's first row (fprop / dgrad)
         int q0 = 0, p0 = 0, img0 = 0;
         if (p.mode == MODE_FPROP || p.mode == MODE_DGRAD || p.mode == MODE_DGRAD_STRIDED) {
-          q0 = m0 % p.Wout;
-          const int t = m0 / p.Wout;
-          p0 = t % p.Hout;
-          img0 = t / p.Hout;
+          q0 = m0 % gW;
+          const int t = m0 / gW;
+          p0 = t % gH;
+          img0 = t / gH;
         }
         const int cblocks = (p.C + BK - 1) / BK;   // channel tail: TMA zero-fills c >= C, so the overhang multiplies by 0
         for (int i = 0; i < nkb; ++i) {
@@ -144,29 +162,29 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           // this CTA's share of the B tile: all BN columns, or the crank-th half of them in pair mode
           const int bn_cta = p.BN / p.cluster, n_off = (int)crank * bn_cta, regions = bn_cta / 64;
           if (p.mode == MODE_GEMM) {
-            if (!p.a_mn) LD2(&tmA, sa, kb * BK, m0 - p.a_shift);
-            else { LD2(&tmA, sa, m0, kb * BK); LD2(&tmA, sa + 8192, m0 + 64, kb * BK); }
+            if (!p.a_mn) LD2(mapA, sa, kb * BK, m0);
+            else { LD2(mapA, sa, m0, kb * BK); LD2(mapA, sa + 8192, m0 + 64, kb * BK); }
             if (!p.b_mn) LD2(&tmB, sb, kb * BK, n0 + n_off);
             else for (int j = 0; j < regions; ++j) LD2(&tmB, sb + j * 8192, n0 + n_off + j * 64, kb * BK);
           } else if (p.mode == MODE_FPROP) {
             const int tap = kb / cblocks, cb = kb % cblocks;
             const int r = tap / p.S, s = tap % p.S;
-            LDI(&tmA, sa, cb * BK, q0 * p.stride - p.pad_w, p0 * p.stride - p.pad_h, img0, s * p.dil, r * p.dil);
+            LDI(mapA, sa, cb * BK, q0 * p.stride - p.pad_w, p0 * p.stride - p.pad_h, img0, s * p.dil, r * p.dil);
             LD2(&tmB, sb, tap * p.C + cb * BK, n0 + n_off);
           } else if (p.mode == MODE_DGRAD) {
             // A = im2col(dy) with pad' = (R-1) - pad, taps (r'', s''); B = W[k][r][s][c] with r = R-1-r'', MN-major
             const int tap = kb / cblocks, cb = kb % cblocks;       // cblocks = ceil(Cout/64) here
             const int rr = tap / p.S, ss = tap % p.S;
-            LDI(&tmA, sa, cb * BK, q0 - p.pad_w, p0 - p.pad_h, img0, ss, rr);
+            LDI(mapA, sa, cb * BK, q0 - p.pad_w, p0 - p.pad_h, img0, ss, rr);
             const int r = p.R - 1 - rr, s = p.S - 1 - ss;
             const int col = (r * p.S + s) * p.Cin_total + n0 + n_off;
             for (int j = 0; j < regions; ++j) LD2(&tmB, sb + j * 8192, col + j * 64, cb * BK);
           } else if (p.mode == MODE_DGRAD_STRIDED) {
             // rows = (n, h', w') of one parity class; dy row = h' + lower_h + (nr-1-i) for filter row r = r0 + st*i
             const int tap = kb / cblocks, cb = kb % cblocks;
-            const int ir = tap / p.ns, is = tap % p.ns;
-            LDI(&tmA, sa, cb * BK, q0 + p.lower_w, p0 + p.lower_h, img0, p.ns - 1 - is, p.nr - 1 - ir);
-            const int r = p.r0 + p.st * ir, s = p.s0 + p.st * is;
+            const int ir = tap / g_ns, is = tap % g_ns;
+            LDI(mapA, sa, cb * BK, q0 + g_lower_w, p0 + g_lower_h, img0, g_ns - 1 - is, g_nr - 1 - ir);
+            const int r = g_r0 + p.st * ir, s = g_s0 + p.st * is;
             const int col = (r * p.S + s) * p.Cin_total + n0 + n_off;
             for (int j = 0; j < regions; ++j) LD2(&tmB, sb + j * 8192, col + j * 64, cb * BK);
           } else {  // MODE_WGRAD: reduction over output pixels; kb = pixel chunk of 64
@@ -174,8 +192,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int q = pix % p.Wout;
             const int t = pix / p.Wout;
             const int pp = t % p.Hout, img = t / p.Hout;
-            LD2(&tmA, sa, m0, pix);
-            LD2(&tmA, sa + 8192, m0 + 64, pix);
+            LD2(mapA, sa, m0, pix);
+            LD2(mapA, sa + 8192, m0 + 64, pix);
             const int r = tap_fixed / p.S, s = tap_fixed % p.S;
             for (int j = 0; j < regions; ++j)
               LDI(&tmB, sb + j * 8192, cblk_fixed * p.BN + n_off + j * 64, q * p.stride - p.pad_w, pp * p.stride - p.pad_h,
@@ -195,11 +213,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (elect_one()) {
           const uint32_t sa = smem_u32(smem + (size_t)st * stage_bytes);
           const uint32_t sb = sa + a_bytes;
-          // Row-shifted view of the A stage: the descriptor simply starts a_shift rows (128 B each) in, base_offset
-          // stays 0.  Measured on B200: the 128B swizzle is a function of the absolute shared-memory address, so a
-          // start that is not 1024 B aligned still de-swizzles what TMA wrote (setting base_offset = (addr>>7)&7
-          // gives wrong results).  This is what lets one halo tile serve all taps of a filter.
-          const uint64_t adesc = make_desc(sa + (uint32_t)p.a_shift * 128u, a_lbo, 1024);
+          const uint64_t adesc = make_desc(sa, a_lbo, 1024);
           const uint64_t bdesc = make_desc(sb, b_lbo, 1024);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
@@ -222,14 +236,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       tc_fence_after();
       const int quarter = warp & 3;                      // TMEM lane quarter this warp may access
       const int row = m0 + quarter * 32 + lane;
-      const bool row_ok = row < p.M;
+      const bool row_ok = row < gM;
       int col_base = n0;
       long long out_off = 0;
       long long out_row = row;
       if (p.mode == MODE_DGRAD_STRIDED && row_ok) {      // scatter to (n, st*h'+ph, st*w'+pw) of the full-resolution dx
-        const int wq = row % p.Wout, t = row / p.Wout;
-        const int hq = t % p.Hout, img = t / p.Hout;
-        out_row = ((long long)img * p.Hfull + (long long)p.st * hq + p.ph) * p.Wfull + (long long)p.st * wq + p.pw;
+        const int wq = row % gW, t = row / gW;
+        const int hq = t % gH, img = t / gH;
+        out_row = ((long long)img * p.Hfull + (long long)p.st * hq + g_ph) * p.Wfull + (long long)p.st * wq + g_pw;
       }
       if (p.mode == MODE_WGRAD) { col_base = cblk_fixed * p.BN; out_off = (long long)tap_fixed * p.Cin_total; }
       for (int c = 0; c < p.BN; c += 32) {
@@ -297,6 +311,22 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       tc_fence_before();
     }
+  } else if (multi && warp >= 2) {
+    // a parity class no filter tap reaches (e.g. three of the four classes of a 1x1 stride-2 convolution): its input
+    // gradient is exactly zero, written here instead of by a memset over the whole tensor
+    const int row = m0 + (warp & 3) * 32 + lane;
+    if (row < gM) {
+      const int wq = row % gW, t = row / gW;
+      const int hq = t % gH, img = t / gH;
+      const long long out_row = ((long long)img * p.Hfull + (long long)p.st * hq + g_ph) * p.Wfull + (long long)p.st * wq + g_pw;
+      __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + out_row * p.ldd + n0;
+      const int ncols = min(p.BN, p.N - n0);
+      if ((ncols & 7) == 0 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+        for (int j = 0; j < ncols; j += 8) *reinterpret_cast<uint4*>(dst + j) = make_uint4(0u, 0u, 0u, 0u);
+      } else {
+        for (int j = 0; j < ncols; ++j) dst[j] = __float2bfloat16_rn(0.f);
+      }
+    }
   }
   __syncthreads();
   if (p.stats && nkb > 0) {
@@ -331,11 +361,14 @@ int want_cluster(int m_tiles, int BN, int b_mn) {
   return 2;
 }
 
-int launch(const CUtensorMap& a, const CUtensorMap& b, TcParams p, dim3 grid, cudaStream_t st) {
+int launch(const CUtensorMap& a, const CUtensorMap& b, TcParams p, dim3 grid, cudaStream_t st,
+           const ExtraMaps* extra = nullptr) {
+  static const ExtraMaps no_extra = {};
+  const ExtraMaps& x = extra ? *extra : no_extra;
   if (p.cluster < 1) p.cluster = 1;
   if (p.cluster == 2) p.idesc = (p.idesc & ~(0x1Fu << 24)) | ((uint32_t)(2 * BM >> 4) << 24);   // UMMA M = 256 across the pair
   p.stages = default_stages(p.BN / p.cluster, p.kb_per_split);
-  const int smem = p.stages * (A_STAGE_BYTES + (p.a_shift ? 2048 : 0) + (p.BN / p.cluster) * BK * 2) + 1024;
+  const int smem = p.stages * (A_STAGE_BYTES + (p.BN / p.cluster) * BK * 2) + 1024;
   static int configured = 0;
   if (configured < smem) {
     cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 1024);
@@ -345,7 +378,7 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, TcParams p, dim3 grid, cu
     configured = 200 * 1024 + 1024;
   }
   if (p.cluster == 1) {
-    tc_gemm_kernel<false><<<grid, kThreads, smem, st>>>(a, b, p);
+    tc_gemm_kernel<false><<<grid, kThreads, smem, st>>>(a, b, x, p);
     return (int)cudaGetLastError();
   }
   grid.x = (grid.x + 1) / 2 * 2;              // CTA pairs along M; a padding CTA only sees out-of-range rows
@@ -356,7 +389,7 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, TcParams p, dim3 grid, cu
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  return (int)cudaLaunchKernelEx(&cfg, tc_gemm_kernel<true>, a, b, p);
+  return (int)cudaLaunchKernelEx(&cfg, tc_gemm_kernel<true>, a, b, x, p);
 }
 
 int pick_bn(int n) {
@@ -393,10 +426,9 @@ MPB_API int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias
   p.idesc = make_idesc(p.BN, a_mn, b_mn);
   p.out_mode = out_mode; p.D = D; p.ldd = ldd; p.bias = bias; p.stats = (splitk == 1) ? stats : nullptr;
   CUtensorMap ta, tb;
-  p.a_shift = a_mn ? 0 : env_int("MPB_TC_ASHIFT", 0);
-  rc = a_mn ? make_map_2d(&ta, A, K, M, lda, 64, 64) : make_map_2d(&ta, A, M, K, lda, 64, BM + (p.a_shift ? 16 : 0));
+  rc = a_mn ? make_map_2d(&ta, A, K, M, lda, 64, 64) : make_map_2d(&ta, A, M, K, lda, 64, BM);
   if (rc) return rc;
-  p.cluster = p.a_shift ? 1 : want_cluster((M + BM - 1) / BM, p.BN, b_mn);
+  p.cluster = want_cluster((M + BM - 1) / BM, p.BN, b_mn);
   rc = b_mn ? make_map_2d(&tb, B, K, N, ldb, 64, 64) : make_map_2d(&tb, B, N, K, ldb, 64, p.BN / p.cluster);
   if (rc) return rc - 1000;
   dim3 grid((M + BM - 1) / BM, (N + p.BN - 1) / p.BN, (p.num_kb + p.kb_per_split - 1) / p.kb_per_split);
@@ -455,42 +487,74 @@ MPB_API int mpb_tc_conv_dgrad(const void* dy, const void* w, void* dx, int N, in
   return launch(ta, tb, p, grid, (cudaStream_t)stream);
 }
 
-// dx for strided convolutions (stride >= 2): one launch per output parity class; positions that no filter tap
-// reaches (e.g. 1x1 stride 2) stay zero (dx is cleared first).
+// dx for strided convolutions (stride >= 2), decomposed by output parity class (ph, pw): each class is a dense
+// stride-1 problem over the filter taps r = r0 + stride*i, s = s0 + stride*j that reach it.  Stride 2 (every strided
+// convolution with a data gradient in the zoo) runs as ONE launch: blockIdx.z selects the class, classes no tap
+// reaches write their zeros themselves, so there is no memset and no per-class launch.  Other strides keep the
+// per-class loop over a cleared dx.
 MPB_API int mpb_tc_conv_dgrad_strided(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int K, int R,
                                       int S, int P, int Q, int stride, int pad_h, int pad_w, void* stream) {
   int rc = load_driver_fns();
   if (rc) return rc;
   if (K % 8 != 0 || C % 8 != 0 || stride < 2) return -2;
   cudaStream_t st = (cudaStream_t)stream;
-  MPB_CUDA(cudaMemsetAsync(dx, 0, (size_t)N * H * W * C * 2, st));
   CUtensorMap tb;
   rc = make_map_2d(&tb, w, K, (long long)R * S * C, (long long)R * S * C, 64, 64);
   if (rc) return rc - 1000;
+  const bool fused = (stride == 2) && env_int("MPB_TC_DGRAD_FUSED", 1) != 0;
+  if (!fused) MPB_CUDA(cudaMemsetAsync(dx, 0, (size_t)N * H * W * C * 2, st));
+  TcParams base;
+  memset(&base, 0, sizeof(base));
+  base.mode = MODE_DGRAD_STRIDED; base.N = C; base.BN = (C > 64) ? 128 : 64; base.a_mn = 0; base.b_mn = 1;
+  base.idesc = make_idesc(base.BN, 0, 1);
+  base.out_mode = OUT_BF16; base.D = dx; base.ldd = C;
+  base.C = K; base.R = R; base.S = S; base.Cin_total = C; base.st = stride; base.Hfull = H; base.Wfull = W;
+  CUtensorMap maps[4];
+  int max_tiles = 0, nmaps = 0;
   for (int ph = 0; ph < stride; ++ph)
     for (int pw = 0; pw < stride; ++pw) {
       const int Hp = (H - ph + stride - 1) / stride, Wp = (W - pw + stride - 1) / stride;
       const int r0 = (ph + pad_h) % stride, s0 = (pw + pad_w) % stride;
       const int nr = r0 < R ? (R - r0 + stride - 1) / stride : 0, ns = s0 < S ? (S - s0 + stride - 1) / stride : 0;
-      if (Hp <= 0 || Wp <= 0 || nr == 0 || ns == 0) continue;
-      TcParams p;
-      memset(&p, 0, sizeof(p));
-      p.mode = MODE_DGRAD_STRIDED; p.M = N * Hp * Wp; p.N = C; p.BN = (C > 64) ? 128 : 64; p.a_mn = 0; p.b_mn = 1;
-      p.num_kb = nr * ns * ((K + 63) / 64); p.kb_per_split = p.num_kb;
-      p.idesc = make_idesc(p.BN, 0, 1);
-      p.out_mode = OUT_BF16; p.D = dx; p.ldd = C;
-      p.C = K; p.R = R; p.S = S; p.Hout = Hp; p.Wout = Wp; p.Cin_total = C;
-      p.st = stride; p.ph = ph; p.pw = pw; p.r0 = r0; p.s0 = s0; p.nr = nr; p.ns = ns; p.Hfull = H; p.Wfull = W;
-      p.lower_h = (ph + pad_h - r0) / stride - (nr - 1);
-      p.lower_w = (pw + pad_w - s0) / stride - (ns - 1);
+      const bool empty = (nr == 0 || ns == 0);
+      if (Hp <= 0 || Wp <= 0) { if (fused) return -2; continue; }
+      if (empty && !fused) continue;
+      TcParams::StridedClass c;
+      c.M = N * Hp * Wp; c.Hout = Hp; c.Wout = Wp; c.ph = ph; c.pw = pw; c.r0 = r0; c.s0 = s0; c.nr = nr; c.ns = ns;
+      c.num_kb = empty ? 0 : nr * ns * ((K + 63) / 64);
+      c.lower_h = empty ? 0 : (ph + pad_h - r0) / stride - (nr - 1);
+      c.lower_w = empty ? 0 : (pw + pad_w - s0) / stride - (ns - 1);
       CUtensorMap ta;   // base pixel h' + lower_h for h' in [0, Hp): bounding box [lower, P + upper) with Hp positions
-      rc = make_map_im2col(&ta, dy, N, P, Q, K, p.lower_w, p.lower_h, Wp - Q + p.lower_w, Hp - P + p.lower_h, 1, BM);
-      if (rc) return rc;
+      if (!empty) {
+        rc = make_map_im2col(&ta, dy, N, P, Q, K, c.lower_w, c.lower_h, Wp - Q + c.lower_w, Hp - P + c.lower_h, 1, BM);
+        if (rc) return rc;
+      } else {
+        ta = tb;        // never dereferenced: a class without taps issues no loads
+      }
+      if (fused) {
+        base.cls[nmaps] = c;
+        maps[nmaps++] = ta;
+        max_tiles = max(max_tiles, (c.M + BM - 1) / BM);
+        continue;
+      }
+      TcParams p = base;
+      p.M = c.M; p.Hout = Hp; p.Wout = Wp; p.num_kb = c.num_kb; p.kb_per_split = c.num_kb;
+      p.ph = ph; p.pw = pw; p.r0 = r0; p.s0 = s0; p.nr = nr; p.ns = ns; p.lower_h = c.lower_h; p.lower_w = c.lower_w;
       dim3 grid((p.M + BM - 1) / BM, (C + p.BN - 1) / p.BN, 1);
       rc = launch(ta, tb, p, grid, st);
       if (rc) return rc;
     }
-  return 0;
+  if (!fused) return 0;
+  base.nclass = nmaps;                       // 4
+  base.M = base.cls[0].M; base.Hout = base.cls[0].Hout; base.Wout = base.cls[0].Wout;
+  int kb_max = 1;
+  for (int i = 0; i < nmaps; ++i) kb_max = max(kb_max, base.cls[i].num_kb);
+  base.num_kb = kb_max; base.kb_per_split = kb_max;          // sizes the smem ring; each CTA uses its class's count
+  ExtraMaps extra;
+  for (int i = 1; i < 4; ++i) extra.m[i - 1] = maps[i < nmaps ? i : 0];
+  base.cluster = want_cluster(max_tiles, base.BN, 1);
+  dim3 grid(max_tiles, (C + base.BN - 1) / base.BN, nmaps);
+  return launch(maps[0], tb, base, grid, st, &extra);
 }
 
 // dw[K,R,S,C] (fp32, pre-zeroed) += sum over pixels dy[n,p,q,k] * x[n, p*stride+r-pad, q*stride+s-pad, c]

@@ -44,167 +44,6 @@ struct HaloParams {
   const float* bias; float* stats;
 };
 
-__global__ void __launch_bounds__(kThreads, 2)
-tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const HaloParams p) {
-  extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* smem_b = smem + (size_t)p.a_stages * p.a_stage_bytes;
-  __shared__ uint64_t full_a[4], empty_a[4], full_b[8], empty_b[8], tmem_full_bar;
-  __shared__ uint32_t tmem_base_smem;
-  __shared__ float stat_smem[2][256];
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int t = blockIdx.x;
-  const int tw = t % p.tiles_w; t /= p.tiles_w;
-  const int th = t % p.tiles_h;
-  const int img = t / p.tiles_h;
-  const int p0 = th * p.TR, j0 = tw * p.TW;
-  const int n0 = blockIdx.y * p.BN;
-  const int cblocks = (p.Ci + BK - 1) / BK, taps = p.R * p.S;
-  uint32_t tmem_cols = 32;
-  while ((int)tmem_cols < p.BN) tmem_cols <<= 1;
-
-  if (threadIdx.x == 0) {
-    prefetch_tmap(&tmA);
-    prefetch_tmap(&tmB);
-    for (int i = 0; i < p.a_stages; ++i) { mbar_init(&full_a[i], 1); mbar_init(&empty_a[i], 1); }
-    for (int i = 0; i < p.b_stages; ++i) { mbar_init(&full_b[i], 1); mbar_init(&empty_b[i], 1); }
-    mbar_init(&tmem_full_bar, 1);
-    fence_barrier_init();
-  }
-  if (p.stats) for (int j = threadIdx.x; j < 256; j += blockDim.x) { stat_smem[0][j] = 0.f; stat_smem[1][j] = 0.f; }
-  if (warp == 1) tmem_alloc(&tmem_base_smem, tmem_cols);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = tmem_base_smem;
-
-  if (warp == 0) {
-    // ================================ TMA producer ================================
-    if (elect_one()) {
-      int ib = 0;
-      for (int cb = 0; cb < cblocks; ++cb) {
-        const int sa = cb % p.a_stages;
-        mbar_wait(&empty_a[sa], ((cb / p.a_stages) & 1) ^ 1);
-        mbar_expect_tx(&full_a[sa], (uint32_t)p.a_box_bytes);
-        tma_load_4d(&tmA, &full_a[sa], smem + (size_t)sa * p.a_stage_bytes, cb * BK, j0 - p.pw, p0 - p.ph, img);
-        for (int tap = 0; tap < taps; ++tap, ++ib) {
-          const int sb = ib % p.b_stages;
-          mbar_wait(&empty_b[sb], ((ib / p.b_stages) & 1) ^ 1);
-          mbar_expect_tx(&full_b[sb], (uint32_t)p.b_stage_bytes);
-          uint8_t* dst = smem_b + (size_t)sb * p.b_stage_bytes;
-          if (!p.b_mn) {
-            tma_load_2d(&tmB, &full_b[sb], dst, tap * p.Ci + cb * BK, n0);        // W[Co][R*S*Ci], K-major
-          } else {
-            const int r = tap / p.S, s = tap % p.S;
-            const int wt = p.flip ? ((p.R - 1 - r) * p.S + (p.S - 1 - s)) : tap;   // dgrad walks the filter backwards
-            for (int j = 0; j < p.BN / 64; ++j)
-              tma_load_2d(&tmB, &full_b[sb], dst + j * 8192, wt * p.w_cols + n0 + j * 64, cb * BK);
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ================================ MMA issuer ================================
-    const uint32_t b_lbo = p.b_mn ? 8192u : 16u, b_step = p.b_mn ? 128u : 2u;
-    int ib = 0;
-    for (int cb = 0; cb < cblocks; ++cb) {
-      const int sa = cb % p.a_stages;
-      mbar_wait(&full_a[sa], (cb / p.a_stages) & 1);
-      const uint32_t abase = smem_u32(smem + (size_t)sa * p.a_stage_bytes);
-      for (int tap = 0; tap < taps; ++tap, ++ib) {
-        const int sb = ib % p.b_stages;
-        mbar_wait(&full_b[sb], (ib / p.b_stages) & 1);
-        tc_fence_after();
-        if (elect_one()) {
-          const int r = tap / p.S, s = tap % p.S;
-          // tap (r, s) = the halo array shifted by r rows of `pitch` pixels and s pixels (128 B per pixel)
-          const uint64_t adesc = make_desc(abase + (uint32_t)(r * p.pitch + s) * 128u, 16u, 1024);
-          const uint64_t bdesc = make_desc(smem_u32(smem_b + (size_t)sb * p.b_stage_bytes), b_lbo, 1024);
-#pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            umma_bf16(tmem_base, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(b_step * k), p.idesc, (cb | tap | k) != 0);
-          umma_commit(&empty_b[sb]);
-          if (tap == taps - 1) {
-            umma_commit(&empty_a[sa]);                       // the halo tile is free once its last tap retired
-            if (cb == cblocks - 1) umma_commit(&tmem_full_bar);
-          }
-        }
-        __syncwarp();
-      }
-    }
-  } else {
-    // ================================ epilogue ================================
-    mbar_wait(&tmem_full_bar, 0);
-    tc_fence_after();
-    const int quarter = warp & 3;
-    const int m = quarter * 32 + lane;                       // GEMM row = position in the padded output tile
-    const int tr = m / p.pitch, j = m % p.pitch;
-    const bool row_ok = tr < p.TR && j < p.TW && (p0 + tr) < p.Ho && (j0 + j) < p.Wo;
-    const long long pix = ((long long)img * p.Ho + p0 + tr) * p.Wo + j0 + j;
-    for (int c = 0; c < p.BN; c += 32) {
-      uint32_t rr[32];
-      tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c, rr);
-      float v[32];
-#pragma unroll
-      for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(rr[q]);
-      if (p.bias) {
-#pragma unroll
-        for (int q = 0; q < 32; ++q) if (n0 + c + q < p.Co) v[q] += p.bias[n0 + c + q];
-      }
-      if (p.stats) {
-        float s1[32], s2[32];
-#pragma unroll
-        for (int q = 0; q < 32; ++q) { const float x = row_ok ? v[q] : 0.f; s1[q] = x; s2[q] = x * x; }
-#pragma unroll
-        for (int off = 16; off >= 1; off >>= 1) {
-          const bool upper = (lane & off) != 0;
-#pragma unroll
-          for (int q = 0; q < off; ++q) {
-            const float send1 = upper ? s1[q] : s1[q + off], send2 = upper ? s2[q] : s2[q + off];
-            const float keep1 = upper ? s1[q + off] : s1[q], keep2 = upper ? s2[q + off] : s2[q];
-            s1[q] = keep1 + __shfl_xor_sync(0xffffffffu, send1, off);
-            s2[q] = keep2 + __shfl_xor_sync(0xffffffffu, send2, off);
-          }
-        }
-        atomicAdd(&stat_smem[0][c + lane], s1[0]);
-        atomicAdd(&stat_smem[1][c + lane], s2[0]);
-      }
-      if (row_ok) {
-        const int ncols = min(32, p.Co - (n0 + c));
-        if (ncols > 0) {
-          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.D) + pix * p.ldd + n0 + c;
-          if (ncols == 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-            for (int q = 0; q < 32; q += 8) {
-              uint4 u;
-              __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&u);
-              h[0] = __floats2bfloat162_rn(v[q], v[q + 1]); h[1] = __floats2bfloat162_rn(v[q + 2], v[q + 3]);
-              h[2] = __floats2bfloat162_rn(v[q + 4], v[q + 5]); h[3] = __floats2bfloat162_rn(v[q + 6], v[q + 7]);
-              *reinterpret_cast<uint4*>(dst + q) = u;
-            }
-          } else {
-            for (int q = 0; q < ncols; ++q) dst[q] = __float2bfloat16_rn(v[q]);
-          }
-        }
-      }
-    }
-    tc_fence_before();
-  }
-  __syncthreads();
-  if (p.stats) {
-    for (int q = threadIdx.x; q < p.BN; q += blockDim.x) {
-      if (n0 + q < p.Co) {
-        atomicAdd(p.stats + n0 + q, stat_smem[0][q]);
-        atomicAdd(p.stats + p.Co + n0 + q, stat_smem[1][q]);
-      }
-    }
-  }
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, tmem_cols);
-  }
-}
 
 // ------------------------------------------------------------------------------------------------------------
 // Persistent variant for layers whose whole filter bank (all taps x channel blocks of this CTA's BN output channels)
@@ -469,20 +308,14 @@ int launch_halo(const void* in, const void* w, void* out, const float* bias, flo
   p.tiles_h = (Ho + p.TR - 1) / p.TR; p.tiles_w = (Wo + p.TW - 1) / p.TW;
   p.BN = (Co > 64) ? 128 : 64; p.b_mn = b_mn; p.flip = flip; p.w_cols = w_cols;
   int bn_p = 0, a_st_p = 0;
-  const bool persistent = env_int("MPB_HALO_PERSIST", 1) != 0 && plan_persistent(Ci, Co, R, S, Ho, Wo, &bn_p, &a_st_p);
-  if (persistent) p.BN = bn_p;
+  if (!plan_persistent(Ci, Co, R, S, Ho, Wo, &bn_p, &a_st_p)) return -2;    // callers check mpb_tc_halo_persistent_ok
+  p.BN = bn_p;
   p.idesc = make_idesc(p.BN, 0, b_mn);
   const int box_h = p.TR + R - 1;
   if (p.pitch > 256 || box_h > 256) return -2;
   p.a_box_bytes = box_h * p.pitch * 128;
   p.a_stage_bytes = (p.a_box_bytes + 1023) / 1024 * 1024;
   p.b_stage_bytes = p.BN * BK * 2;
-  p.a_stages = 2;
-  p.b_stages = env_int("MPB_HALO_BSTAGES", 4);
-  if (p.b_stages > 8) p.b_stages = 8;
-  while (p.b_stages > 2 && p.a_stages * p.a_stage_bytes + p.b_stages * p.b_stage_bytes + 2048 > 110 * 1024) --p.b_stages;
-  const int smem = p.a_stages * p.a_stage_bytes + p.b_stages * p.b_stage_bytes + 2048;   // +1 KB align, +1 KB tap overrun
-  if (smem > 200 * 1024) return -3;
   p.D = out; p.ldd = Co; p.bias = bias; p.stats = stats;
   CUtensorMap ta, tb;
   rc = make_map_nhwc_tiled(&ta, in, N, Hi, Wi, Ci, p.pitch, box_h, xs_w, xs_h, xs_n);
@@ -492,28 +325,21 @@ int launch_halo(const void* in, const void* w, void* out, const float* bias, flo
   if (rc) return rc - 1000;
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(tc_halo_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 210 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(tc_halo_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 210 * 1024);
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
-  if (persistent) {
-    const int cblocks = (Ci + BK - 1) / BK;
-    const long long wbytes = (long long)cblocks * R * S * p.b_stage_bytes;
-    const int n_tiles_y = (Co + p.BN - 1) / p.BN;
-    p.a_stages = a_st_p;
-    const int smem_p = p.a_stages * p.a_stage_bytes + (int)wbytes + 2048;
-    const int num_tiles = N * p.tiles_h * p.tiles_w;
-    int ctas = kSMs / n_tiles_y;
-    if (ctas < 1) ctas = 1;
-    if (ctas > num_tiles) ctas = num_tiles;
-    dim3 gridp((unsigned)ctas, (unsigned)n_tiles_y, 1);
-    tc_halo_persist_kernel<<<gridp, kThreadsPersist, smem_p, st>>>(ta, tb, p, num_tiles);
-    return (int)cudaGetLastError();
-  }
-  dim3 grid((unsigned)(N * p.tiles_h * p.tiles_w), (unsigned)((Co + p.BN - 1) / p.BN), 1);
-  tc_halo_kernel<<<grid, kThreads, smem, st>>>(ta, tb, p);
+  const int cblocks = (Ci + BK - 1) / BK;
+  const long long wbytes = (long long)cblocks * R * S * p.b_stage_bytes;
+  const int n_tiles_y = (Co + p.BN - 1) / p.BN;
+  p.a_stages = a_st_p;
+  const int smem_p = p.a_stages * p.a_stage_bytes + (int)wbytes + 2048;
+  const int num_tiles = N * p.tiles_h * p.tiles_w;
+  int ctas = kSMs / n_tiles_y;
+  if (ctas < 1) ctas = 1;
+  if (ctas > num_tiles) ctas = num_tiles;
+  dim3 gridp((unsigned)ctas, (unsigned)n_tiles_y, 1);
+  tc_halo_persist_kernel<<<gridp, kThreadsPersist, smem_p, st>>>(ta, tb, p, num_tiles);
   return (int)cudaGetLastError();
 }
 

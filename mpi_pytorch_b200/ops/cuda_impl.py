@@ -177,7 +177,13 @@ class _ConvFn(torch.autograd.Function):
             gx = tc.conv_dgrad(gy, w, x.shape, stride, padding)
             need_x = False
         if need_w and ctx.xs2d is not None:
-            gw = tc.conv_wgrad_stem(gy, ctx.xs2d, x.shape, w.shape, padding).to(wdtype)
+            wp = ctx.weight_param
+            if wp is not None and wp.grad is not None and wp.grad.dtype == torch.float32 \
+                    and wp.grad.permute(0, 2, 3, 1).is_contiguous():
+                tc.conv_wgrad_stem(gy, ctx.xs2d, x.shape, w.shape, padding, out=wp.grad)   # += the arena slot
+                wp._mpb_grad_ready(wp)
+            else:
+                gw = tc.conv_wgrad_stem(gy, ctx.xs2d, x.shape, w.shape, padding).to(wdtype)
             need_w = False
         if need_w and ctx.xcol is not None:
             gw = tc.conv_wgrad_im2col(gy, ctx.xcol, w.shape).to(wdtype)
@@ -250,7 +256,11 @@ class _LinearFn(torch.autograd.Function):
             if ctx.needs_input_grad[1]:
                 gw = (gy.t() @ x).to(wdtype)
         if has_bias and ctx.needs_input_grad[2]:
-            gb = gy.float().sum(dim=0)
+            k = gy.shape[1]
+            if k % 8 == 0 and k <= 2048 and gy.dtype in (torch.bfloat16, torch.float32):
+                gb = bn_stats(gy.view(gy.shape[0], k, 1, 1))[:k]     # the column-sum kernel conv biases use
+            else:
+                gb = gy.float().sum(dim=0)
         return gx, gw, gb
 
 

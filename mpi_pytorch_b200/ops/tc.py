@@ -117,9 +117,6 @@ HALO = os.environ.get("MPB_TC_HALO", "1").lower() not in ("0", "false", "off")
 HALO_MIN_EFF = float(os.environ.get("MPB_TC_HALO_MIN_EFF", "0.6"))
 
 
-HALO_STREAMING = os.environ.get("MPB_TC_HALO_STREAMING", "0") == "1"   # also use the non-persistent halo kernel
-
-
 def halo_ok(out_h: int, out_w: int, r: int, s: int, stride, ci: int = 0, co: int = 0) -> bool:
     """Stride-1 filters larger than 1x1 whose padded output rows tile the 128 GEMM rows well enough run on the
     halo-tile kernel (activation tile fetched once per channel block instead of once per tap)."""
@@ -127,8 +124,6 @@ def halo_ok(out_h: int, out_w: int, r: int, s: int, stride, ci: int = 0, co: int
         return False
     if float(_LIB.mpb_tc_halo_efficiency(c_int(out_h), c_int(out_w), c_int(r), c_int(s))) < HALO_MIN_EFF:
         return False
-    if HALO_STREAMING:
-        return True
     return bool(_LIB.mpb_tc_halo_persistent_ok(c_int(ci), c_int(co), c_int(r), c_int(s), c_int(out_h), c_int(out_w)))
 
 
@@ -287,7 +282,7 @@ def _s2d_index(c: int, pad: int, device):
     key = (c, pad, str(device))
     if key not in _S2D_IDX:
         off, zero = pad % 2, 49 * c
-        fwd = torch.full((4 * 64,), zero, dtype=torch.int64)
+        fwd = torch.full((4 * 64,), -1, dtype=torch.int64)      # -1: a zero column (mpb_gather_cols)
         inv = torch.zeros(49 * c, dtype=torch.int64)
         for a in range(4):
             for a2 in range(4):
@@ -321,8 +316,13 @@ def conv_fprop_stem(x, w, bias, padding, want_stats=False):
                            c_void_p(_stream()))
     _check(rc, "mpb_s2d_stem")
     fwd, _ = _s2d_index(c, padding[0], x.device)
-    wk = w.permute(0, 2, 3, 1).reshape(k, 49 * c)
-    w2 = torch.cat([wk, wk.new_zeros(k, 1)], dim=1)[:, fwd].contiguous()             # [K][4 taps][64]
+    wk = w.permute(0, 2, 3, 1)                       # KRSC view: free for a channels-last filter (the bf16 shadow)
+    if not wk.is_contiguous():
+        wk = wk.contiguous()
+    w2 = torch.empty((k, 4 * 64), dtype=torch.bfloat16, device=x.device)                # [K][4 taps][64]
+    rc = _LIB.mpb_gather_cols(_p(wk), _p(fwd), _p(w2), c_int(k), c_int(49 * c), c_int(4 * 64),
+                              c_int(0 if wk.dtype == torch.float32 else 1), c_int(1), c_int(0), c_void_p(_stream()))
+    _check(rc, "mpb_gather_cols")
     y = torch.empty((n, k, p, q), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
     stats = _scratch.take(2 * k, x.device)[0] if want_stats else None
     ll = ctypes.c_longlong
@@ -335,9 +335,11 @@ def conv_fprop_stem(x, w, bias, padding, want_stats=False):
     return y, stats, xs
 
 
-def conv_wgrad_stem(gy, xs, x_shape, w_shape, padding) -> torch.Tensor:
+def conv_wgrad_stem(gy, xs, x_shape, w_shape, padding, out=None) -> torch.Tensor:
+    """Filter gradient of the space-to-depth stem.  With ``out`` (the fp32 KRSC slot of the gradient arena, logical
+    shape (K,C,7,7)) the result is ADDED there by the gather kernel and ``out`` is returned."""
     n, c, h, wd, k, p, q, lpad, wp = _s2d_geom(x_shape, w_shape, padding)
-    dw2 = torch.zeros((k, 4 * 64), dtype=torch.float32, device=gy.device)
+    dw2 = _scratch.take(k * 4 * 64, gy.device)[0].view(k, 4 * 64)
     ll = ctypes.c_longlong
     rc = _LIB.mpb_tc_conv_wgrad_halo_strided(_p(gy), _p(xs), _p(dw2), c_int(n), c_int(h // 2), c_int(wp - 3), c_int(64),
                                              c_int(k), c_int(4), c_int(1), c_int(p), c_int(q), c_int(lpad), c_int(0),
@@ -345,4 +347,10 @@ def conv_wgrad_stem(gy, xs, x_shape, w_shape, padding) -> torch.Tensor:
     LAUNCHES["n"] += 1
     _check(rc, "mpb_tc_conv_wgrad_halo_strided")
     _, inv = _s2d_index(c, padding[0], gy.device)
-    return dw2[:, inv].reshape(k, 7, 7, c).permute(0, 3, 1, 2)                      # logical (K,C,R,S)
+    acc = out is not None
+    dst = out.permute(0, 2, 3, 1) if acc else torch.empty((k, 7, 7, c), dtype=torch.float32, device=gy.device)
+    rc = _LIB.mpb_gather_cols(_p(dw2), _p(inv), _p(dst), c_int(k), c_int(4 * 64), c_int(49 * c), c_int(0), c_int(0),
+                              c_int(int(acc)), c_void_p(_stream()))
+    LAUNCHES["n"] += 1
+    _check(rc, "mpb_gather_cols")
+    return out if acc else dst.permute(0, 3, 1, 2)                                  # logical (K,C,R,S)

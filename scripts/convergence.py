@@ -24,7 +24,8 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-N_SAMPLES, CLASSES, HW, BATCH, EPOCHS, LR = 800, 10, 128, 128, 10, 4e-4      # main.py:75-79, utils.py:33-42 (DEBUG sizes)
+N_SAMPLES, CLASSES, HW, BATCH, EPOCHS, LR = 800, 100, 128, 128, 10, 4e-4      # main.py:75-79, utils.py:33-42 (DEBUG sizes)
+SIGNAL = 0.06          # weight of the class template against the noise: small enough that ten epochs are needed
 MEAN, STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
 
 
@@ -32,9 +33,9 @@ def make_data(seed: int = 0):
     """[N,3,HW,HW] fp32 (already normalised like main.py:62-65 would) + int64 labels; CPU, deterministic."""
     g = torch.Generator().manual_seed(1000 + seed)
     labels = torch.randint(0, CLASSES, (N_SAMPLES,), generator=g)
-    templates = torch.rand(CLASSES, 3, 8, 8, generator=g)
+    templates = torch.rand(CLASSES, 3, 16, 16, generator=g)
     up = torch.nn.functional.interpolate(templates, size=(HW, HW), mode="nearest")
-    img = (0.55 * up[labels] + 0.45 * torch.rand(N_SAMPLES, 3, HW, HW, generator=g)).clamp_(0, 1)
+    img = (SIGNAL * up[labels] + (1.0 - SIGNAL) * torch.rand(N_SAMPLES, 3, HW, HW, generator=g)).clamp_(0, 1)
     mean, std = torch.tensor(MEAN).view(1, 3, 1, 1), torch.tensor(STD).view(1, 3, 1, 1)
     return ((img - mean) / std).contiguous(), labels
 
