@@ -127,6 +127,15 @@ float mpb_tc_halo_efficiency(int Ho, int Wo, int R, int S);
 int mpb_tc_halo_persistent_ok(int Ci, int Co, int R, int S, int Ho, int Wo);
 int mpb_tc_conv_fprop_halo(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H, int W,
                            int C, int K, int R, int S, int P, int Q, int pad_h, int pad_w, void* stream);
+/* fprop with an activation epilogue: y = relu?(conv(x, w) + bias).  With BatchNorm folded into w / bias (eval mode:
+ * w' = w * gamma / sqrt(var + eps), bias' = beta - mean * gamma / sqrt(var + eps)) one kernel is the Conv2d + BatchNorm2d
+ * (+ ReLU) triple of a torchvision block (models.py:30-95 build them; evaluation_pipeline.py:155-156 runs them).   */
+int mpb_tc_conv_fprop_act(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H, int W,
+                          int C, int K, int R, int S, int P, int Q, int stride, int pad_h, int pad_w, int dil, int relu,
+                          void* stream);
+int mpb_tc_conv_fprop_halo_act(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H,
+                               int W, int C, int K, int R, int S, int P, int Q, int pad_h, int pad_w, int relu,
+                               void* stream);
 int mpb_tc_conv_dgrad_halo(const void* dy, const void* w, void* dx, int N, int H, int W, int C, int K, int R, int S,
                            int P, int Q, int pad_h, int pad_w, void* stream);
 /* dx for stride >= 2: decomposed into stride^2 output-parity classes, each an implicit GEMM over the taps that reach it. */

@@ -57,6 +57,7 @@ struct TcParams {
   int stages;               // smem ring depth (fewer stages -> more co-resident CTAs per SM)
   // strided dgrad, one launch per output parity class (ph, pw): valid filter taps r = r0 + st*i, s = s0 + st*j
   int st, ph, pw, r0, s0, nr, ns, lower_h, lower_w, Hfull, Wfull;
+  int relu;                 // epilogue: max(x, 0) after the bias (inference: conv + folded BatchNorm + ReLU in one kernel)
   int nclass;               // strided dgrad as ONE launch: blockIdx.z = output parity class, geometry in cls[z]
   struct StridedClass { int M, Hout, Wout, num_kb, ph, pw, r0, s0, nr, ns, lower_h, lower_w; } cls[4];
   int cluster;              // 1, or 2: CTA pair (cta_group::2) computes a 256 x BN tile; each CTA stages its 128 A rows and HALF of B
@@ -256,6 +257,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
           for (int j = 0; j < 32; ++j) if (col_base + c + j < p.N) v[j] += p.bias[col_base + c + j];
         }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+        }
         if (p.stats) {
           // per-column sums over this warp's 32 rows: transpose-reduce (31 shuffles per quantity)
           float s1[32], s2[32];
@@ -437,9 +442,9 @@ MPB_API int mpb_tc_gemm(const void* A, const void* B, void* D, const float* bias
 
 // y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C]) (+bias); NHWC bf16; C % 64 == 0, K % 16 == 0.
 // stats (optional): fp32 [2*K], must be zeroed by the caller; receives per-channel sum / sum of squares of y (fp32).
-MPB_API int mpb_tc_conv_fprop(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H, int W,
-                              int C, int K, int R, int S, int P, int Q, int stride, int pad_h, int pad_w, int dil,
-                              void* stream) {
+MPB_API int mpb_tc_conv_fprop_act(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H,
+                                  int W, int C, int K, int R, int S, int P, int Q, int stride, int pad_h, int pad_w,
+                                  int dil, int relu, void* stream) {
   int rc = load_driver_fns();
   if (rc) return rc;
   if (C % 8 != 0 || K % 8 != 0) return -2;
@@ -448,7 +453,7 @@ MPB_API int mpb_tc_conv_fprop(const void* x, const void* w, void* y, const float
   p.mode = MODE_FPROP; p.M = N * P * Q; p.N = K; p.BN = pick_bn(K);
   p.num_kb = R * S * ((C + 63) / 64); p.kb_per_split = p.num_kb;
   p.idesc = make_idesc(p.BN, 0, 0);
-  p.out_mode = OUT_BF16; p.D = y; p.ldd = K; p.bias = bias; p.stats = stats;
+  p.out_mode = OUT_BF16; p.D = y; p.ldd = K; p.bias = bias; p.stats = stats; p.relu = relu;
   p.C = C; p.R = R; p.S = S; p.Hout = P; p.Wout = Q; p.stride = stride; p.pad_h = pad_h; p.pad_w = pad_w; p.dil = dil;
   CUtensorMap ta, tb;
   rc = make_map_im2col(&ta, x, N, H, W, C, -pad_w, -pad_h, pad_w - (S - 1) * dil, pad_h - (R - 1) * dil, stride, BM);
@@ -458,6 +463,12 @@ MPB_API int mpb_tc_conv_fprop(const void* x, const void* w, void* y, const float
   if (rc) return rc - 1000;
   dim3 grid((p.M + BM - 1) / BM, (K + p.BN - 1) / p.BN, 1);
   return launch(ta, tb, p, grid, (cudaStream_t)stream);
+}
+
+MPB_API int mpb_tc_conv_fprop(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H, int W,
+                              int C, int K, int R, int S, int P, int Q, int stride, int pad_h, int pad_w, int dil,
+                              void* stream) {
+  return mpb_tc_conv_fprop_act(x, w, y, bias, stats, N, H, W, C, K, R, S, P, Q, stride, pad_h, pad_w, dil, 0, stream);
 }
 
 // dx[N,H,W,C] = conv_transpose(dy[N,P,Q,K], w[K,R,S,C]) for stride-1, dilation-1 convolutions (P = H + 2*pad - R + 1).

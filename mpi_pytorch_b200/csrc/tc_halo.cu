@@ -42,6 +42,7 @@ struct HaloParams {
   int a_stages, b_stages, a_stage_bytes, b_stage_bytes, a_box_bytes;
   void* D; long long ldd;
   const float* bias; float* stats;
+  int relu;                 // epilogue: max(x, 0) after the bias
 };
 
 
@@ -192,6 +193,10 @@ tc_halo_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 #pragma unroll
           for (int q = 0; q < 32; ++q) if (n0 + c + q < p.Co) v[q] += p.bias[n0 + c + q];
         }
+        if (p.relu) {
+#pragma unroll
+          for (int q = 0; q < 32; ++q) v[q] = fmaxf(v[q], 0.f);
+        }
         if (p.stats) {
           float s1[32], s2[32];
 #pragma unroll
@@ -297,7 +302,7 @@ bool plan_persistent(int Ci, int Co, int R, int S, int Ho, int Wo, int* BN_out, 
 
 int launch_halo(const void* in, const void* w, void* out, const float* bias, float* stats, int N, int Hi, int Wi, int Ci,
                 int Ho, int Wo, int Co, int R, int S, int ph, int pw, int b_mn, int flip, int w_rows, long long w_cols_total,
-                int w_cols, cudaStream_t st, long long xs_w = 0, long long xs_h = 0, long long xs_n = 0) {
+                int w_cols, cudaStream_t st, long long xs_w = 0, long long xs_h = 0, long long xs_n = 0, int relu = 0) {
   int rc = load_driver_fns();
   if (rc) return rc;
   HaloParams p;
@@ -316,7 +321,7 @@ int launch_halo(const void* in, const void* w, void* out, const float* bias, flo
   p.a_box_bytes = box_h * p.pitch * 128;
   p.a_stage_bytes = (p.a_box_bytes + 1023) / 1024 * 1024;
   p.b_stage_bytes = p.BN * BK * 2;
-  p.D = out; p.ldd = Co; p.bias = bias; p.stats = stats;
+  p.D = out; p.ldd = Co; p.bias = bias; p.stats = stats; p.relu = relu;
   CUtensorMap ta, tb;
   rc = make_map_nhwc_tiled(&ta, in, N, Hi, Wi, Ci, p.pitch, box_h, xs_w, xs_h, xs_n);
   if (rc) return rc;
@@ -361,11 +366,16 @@ MPB_API float mpb_tc_halo_efficiency(int Ho, int Wo, int R, int S) {
 }
 
 // y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C]), stride 1, dilation 1 (P = H + 2*pad_h - R + 1).  stats as in mpb_tc_conv_fprop.
-MPB_API int mpb_tc_conv_fprop_halo(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H,
-                                   int W, int C, int K, int R, int S, int P, int Q, int pad_h, int pad_w, void* stream) {
+MPB_API int mpb_tc_conv_fprop_halo_act(const void* x, const void* w, void* y, const float* bias, float* stats, int N,
+                                       int H, int W, int C, int K, int R, int S, int P, int Q, int pad_h, int pad_w,
+                                       int relu, void* stream) {
   if (C % 8 != 0 || K % 8 != 0) return -2;
   return launch_halo(x, w, y, bias, stats, N, H, W, C, P, Q, K, R, S, pad_h, pad_w, /*b_mn=*/0, /*flip=*/0,
-                     /*w_rows=*/K, /*w_cols_total=*/(long long)R * S * C, /*w_cols=*/0, (cudaStream_t)stream);
+                     /*w_rows=*/K, /*w_cols_total=*/(long long)R * S * C, /*w_cols=*/0, (cudaStream_t)stream, 0, 0, 0, relu);
+}
+MPB_API int mpb_tc_conv_fprop_halo(const void* x, const void* w, void* y, const float* bias, float* stats, int N, int H,
+                                   int W, int C, int K, int R, int S, int P, int Q, int pad_h, int pad_w, void* stream) {
+  return mpb_tc_conv_fprop_halo_act(x, w, y, bias, stats, N, H, W, C, K, R, S, P, Q, pad_h, pad_w, 0, stream);
 }
 
 // Same, with explicit element strides of x between pixels / rows / images.  A pixel stride smaller than C describes

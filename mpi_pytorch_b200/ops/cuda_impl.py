@@ -113,6 +113,10 @@ def prepare_inference(model: torch.nn.Module, dtype: torch.dtype = torch.bfloat1
                     p._mpb_shadow = p.detach().to(dtype).contiguous(memory_format=torch.channels_last)
                 else:
                     p._mpb_shadow = p.detach().to(dtype).contiguous()
+        for m in model.modules():
+            if isinstance(m, torch.nn.Conv2d):
+                m._mpb_fold_ok = True      # weights are frozen from here on: conv_bn_act may fold BatchNorm into them
+                m._mpb_fold = None
     return model.eval()
 
 
@@ -371,9 +375,38 @@ def batch_norm_act(x, bn, residual=None, relu=False, sums=None):
                           bool(relu), bool(bn.training), sums, nbt)
 
 
+FOLDED = {"n": 0}              # conv+BN(+ReLU) calls served by ONE kernel through folded weights (inference)
+
+
+def _folded(conv, bn, dtype):
+    """Eval-mode BatchNorm folded into the convolution: w' = w * g / sqrt(var + eps) per output channel,
+    b' = beta - mean * g / sqrt(var + eps) (+ the conv bias scaled alike).  Built once per (conv, bn) pair of a
+    model that ``prepare_inference`` froze; the fprop kernel then applies b' and the ReLU in its epilogue."""
+    fold = getattr(conv, "_mpb_fold", None)
+    if fold is None or fold[0] is not bn:
+        with torch.no_grad():
+            scale = bn.weight.float() * torch.rsqrt(bn.running_var.float() + bn.eps)
+            w = (conv.weight.float() * scale.view(-1, 1, 1, 1)).to(dtype).contiguous(memory_format=torch.channels_last)
+            b = bn.bias.float() - bn.running_mean.float() * scale
+            if conv.bias is not None:
+                b = b + conv.bias.float() * scale
+        fold = conv._mpb_fold = (bn, w, b.contiguous())
+    return fold[1], fold[2]
+
+
 def conv_bn_act(x, conv, bn, relu=True, residual=None):
     if x.dtype not in (torch.bfloat16, torch.float32):
         x = x.to(torch.bfloat16)
+    if (not bn.training and residual is None and getattr(conv, "_mpb_fold_ok", False) and not torch.is_grad_enabled()
+            and x.dtype == torch.bfloat16 and bn.track_running_stats and bn.affine):
+        tc = _gemm()
+        x = _nhwc(x)
+        stride, padding, dil = _pair(conv.stride), _pair(conv.padding), _pair(conv.dilation)
+        w, b = _folded(conv, bn, x.dtype)
+        if tc.fprop_ok(x, w, stride, padding, dil, int(conv.groups)) and \
+                not tc.stem_s2d_ok(x, w, stride, padding, dil, int(conv.groups)):
+            FOLDED["n"] += 1
+            return tc.conv_fprop(x, w, b, stride, padding, False, relu=relu)[0]
     want_stats = bn.training and _bn_ok_channels(conv.out_channels)
     res = _ConvFn.apply(x, conv.weight, conv.bias, _pair(conv.stride), _pair(conv.padding), _pair(conv.dilation),
                         int(conv.groups), want_stats)

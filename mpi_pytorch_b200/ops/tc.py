@@ -138,20 +138,22 @@ def wgrad_halo_ok(c: int, k: int, r: int, s: int, out_h: int, out_w: int, stride
     return bool(_LIB.mpb_tc_wgrad_halo_ok(c_int(c), c_int(k), c_int(r), c_int(s), c_int(out_h), c_int(out_w)))
 
 
-def conv_fprop(x, w, bias, stride, padding, want_stats=False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+def conv_fprop(x, w, bias, stride, padding, want_stats=False, relu=False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
     n, c, h, wd, k, r, s, p, q = _geom(x.shape, w.shape, stride, padding)
     y = torch.empty((n, k, p, q), dtype=torch.bfloat16, device=x.device, memory_format=torch.channels_last)
     stats = _scratch.take(2 * k, x.device)[0] if want_stats else None
     if halo_ok(p, q, r, s, stride, c, k):
-        rc = _LIB.mpb_tc_conv_fprop_halo(_p(x), _p(w), _p(y), _p(None if bias is None else bias.float()), _p(stats),
-                                         c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r), c_int(s), c_int(p),
-                                         c_int(q), c_int(padding[0]), c_int(padding[1]), c_void_p(_stream()))
+        rc = _LIB.mpb_tc_conv_fprop_halo_act(_p(x), _p(w), _p(y), _p(None if bias is None else bias.float()), _p(stats),
+                                             c_int(n), c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r), c_int(s),
+                                             c_int(p), c_int(q), c_int(padding[0]), c_int(padding[1]), c_int(int(relu)),
+                                             c_void_p(_stream()))
         LAUNCHES["n"] += 1 + int(want_stats)
         _check(rc, "mpb_tc_conv_fprop_halo")
         return y, stats
-    rc = _LIB.mpb_tc_conv_fprop(_p(x), _p(w), _p(y), _p(None if bias is None else bias.float()), _p(stats), c_int(n),
-                                c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r), c_int(s), c_int(p), c_int(q),
-                                c_int(stride[0]), c_int(padding[0]), c_int(padding[1]), c_int(1), c_void_p(_stream()))
+    rc = _LIB.mpb_tc_conv_fprop_act(_p(x), _p(w), _p(y), _p(None if bias is None else bias.float()), _p(stats), c_int(n),
+                                    c_int(h), c_int(wd), c_int(c), c_int(k), c_int(r), c_int(s), c_int(p), c_int(q),
+                                    c_int(stride[0]), c_int(padding[0]), c_int(padding[1]), c_int(1), c_int(int(relu)),
+                                    c_void_p(_stream()))
     LAUNCHES["n"] += 1 + int(want_stats)
     _check(rc, "mpb_tc_conv_fprop")
     return y, stats

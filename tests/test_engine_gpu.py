@@ -157,3 +157,28 @@ def test_bf16_wire_kernel_world1():
         torch.cuda.synchronize()
         assert torch.equal(wire, g.bfloat16())
         assert torch.allclose(p, p2, atol=1e-6) and torch.equal(sh, p.bfloat16())
+
+
+def test_inference_folds_batchnorm_into_the_conv_epilogue():
+    """prepare_inference: Conv2d + eval BatchNorm2d (+ ReLU) of a block runs as ONE fprop kernel (folded weights,
+    bias + ReLU epilogue); logits must match the unfolded eval path (evaluation_pipeline.py:147,155-156)."""
+    from mpi_pytorch_b200 import ops
+    from mpi_pytorch_b200.models import initialize_model
+    torch.manual_seed(3)
+    m, _ = initialize_model("resnet18", 16, False, use_pretrained=False)
+    m = m.cuda().to(memory_format=torch.channels_last)
+    with torch.no_grad():
+        for mod in m.modules():                      # non-trivial statistics, as after training
+            if isinstance(mod, torch.nn.BatchNorm2d):
+                mod.running_mean.normal_(0, 0.2); mod.running_var.uniform_(0.5, 1.5)
+                mod.weight.uniform_(0.5, 1.5); mod.bias.normal_(0, 0.2)
+    x = torch.randn(32, 3, 128, 128, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    m.eval()
+    with torch.no_grad():
+        want = m(x).float()
+        n0 = ops.native().FOLDED["n"]
+        ops.prepare_inference(m, torch.bfloat16)
+        got = m(x).float()
+    assert ops.native().FOLDED["n"] - n0 >= 10       # conv1 of 8 blocks + 3 downsample convs (stem stays unfused)
+    assert torch.allclose(got, want, atol=0.06, rtol=0.05), float((got - want).abs().max())
+    assert (got.argmax(1) == want.argmax(1)).float().mean() > 0.9
