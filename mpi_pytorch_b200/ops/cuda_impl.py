@@ -268,9 +268,45 @@ class _LinearFn(torch.autograd.Function):
         return gx, gw, gb
 
 
+class _LinearPadFn(torch.autograd.Function):
+    """Linear layer whose output width is not a multiple of 8 -- the reference's default head has 64,500 classes
+    (utils.py:39) -- on the tensor-core GEMM: TMA needs 16-byte row strides, so the layer is computed with the class
+    dimension zero-padded to the next multiple of 8 (compute copy of W, logits, their gradient) and sliced back."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        n, k = weight.shape
+        npad = (n + 7) // 8 * 8
+        w = _compute_weight(weight, x.dtype)
+        wp = torch.zeros((npad, k), dtype=x.dtype, device=x.device)
+        wp[:n].copy_(w)
+        bp = None
+        if bias is not None:
+            bp = torch.zeros(npad, dtype=torch.float32, device=x.device)
+            bp[:n].copy_(bias.detach())
+        ctx.save_for_backward(x, wp)
+        ctx.conf = (bias is not None, weight.dtype, n)
+        return _gemm().linear_fwd(x, wp, bp)[:, :n]
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, wp = ctx.saved_tensors
+        has_bias, wdtype, n = ctx.conf
+        tc = _gemm()
+        gp = torch.zeros((gy.shape[0], wp.shape[0]), dtype=x.dtype, device=x.device)
+        gp[:, :n].copy_(gy)
+        gx = tc.linear_dx(gp, wp) if ctx.needs_input_grad[0] else None
+        gw = tc.linear_dw(gp, x)[:n].to(wdtype) if ctx.needs_input_grad[1] else None
+        gb = gy.float().sum(dim=0) if (has_bias and ctx.needs_input_grad[2]) else None
+        return gx, gw, gb
+
+
 def linear(x, w, b):
     if x.dtype not in (torch.bfloat16, torch.float32) or x.dim() != 2:
         return F.linear(x, w.to(x.dtype), None if b is None else b.to(x.dtype))
+    if (w.shape[0] % 8 != 0 and w.shape[1] % 8 == 0 and x.shape[0] % 8 == 0 and x.dtype == torch.bfloat16
+            and _gemm().ENABLED):
+        return _LinearPadFn.apply(x.contiguous(), w, b)
     return _LinearFn.apply(x.contiguous(), w, b)
 
 

@@ -22,6 +22,8 @@ HBM = 6463.0
 def timed(fn, reps=10):
     fn(); fn()
     torch.cuda.synchronize()
+    if os.environ.get("MPB_NCU") == "1":               # under ncu: the two launches above are all that is wanted
+        return 1.0
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     best = 1e9
     for _ in range(reps):

@@ -27,6 +27,7 @@ def _trainer(model, hw, batch, dtype="bf16", lr=0.0, classes=24, **kw):
 def _grads(model, hw, batch, native, dtype="bf16"):
     from mpi_pytorch_b200 import ops
     ops.set_native(native)
+    fb0 = dict(ops.native().FALLBACKS) if native else {}
     try:
         tr = _trainer(model, hw, batch, dtype=dtype)
         for m in tr.model.modules():
@@ -40,7 +41,7 @@ def _grads(model, hw, batch, native, dtype="bf16"):
         torch.cuda.synchronize()
         out = {n: tr.engine.layout.view(tr.engine.grad_arena, p).detach().float().clone()
                for n, p in tr.model.named_parameters() if p.requires_grad}
-        fb = dict(ops.native().FALLBACKS) if native else {}
+        fb = {k: v - fb0.get(k, 0) for k, v in ops.native().FALLBACKS.items() if v != fb0.get(k, 0)} if native else {}
         tr.close()
         return float(loss.detach()), out, fb
     finally:

@@ -189,3 +189,25 @@ def test_stem_conv_via_im2col_gemm(n, c, h, w, k, r, stride, pad):
     assert _rel(stats[:k], yref.sum(dim=(0, 2, 3))) < 1e-4
     dw = tc.conv_wgrad_im2col(gy, xcol, wt.shape)
     assert dw.shape == wf.grad.shape and _rel(dw, wf.grad) < 2e-4
+
+
+def test_linear_head_with_64500_classes_stays_on_the_tensor_core_gemm():
+    """The reference's default head (utils.py:39: 64,500 classes, not a multiple of 8) must not fall back to cuBLAS."""
+    from mpi_pytorch_b200 import ops
+    nat = ops.native()
+    torch.manual_seed(0)
+    x = (torch.randn(64, 512, device="cuda") * 0.5).to(torch.bfloat16).requires_grad_(True)
+    w = (torch.randn(64500, 512, device="cuda") * 0.05).requires_grad_(True)
+    b = torch.randn(64500, device="cuda").requires_grad_(True)
+    before = dict(nat.FALLBACKS)
+    y = nat.linear(x, w, b)
+    gy = torch.randn(64, 64500, device="cuda").to(torch.bfloat16)
+    y.backward(gy)
+    assert dict(nat.FALLBACKS) == before
+    xr, wr = x.detach().float().requires_grad_(True), w.detach().to(torch.bfloat16).float().requires_grad_(True)
+    yr = torch.nn.functional.linear(xr, wr, b.detach())
+    yr.backward(gy.float())
+    assert y.shape == (64, 64500) and torch.allclose(y.float(), yr, atol=0.06, rtol=0.03)
+    assert torch.allclose(x.grad.float(), xr.grad, atol=0.5, rtol=0.03)
+    assert torch.allclose(w.grad, wr.grad, atol=0.15, rtol=0.03)
+    assert torch.allclose(b.grad, gy.float().sum(0), atol=0.1, rtol=0.02)
