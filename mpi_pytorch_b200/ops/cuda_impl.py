@@ -157,7 +157,7 @@ class _ConvFn(torch.autograd.Function):
                                                       want_stats)
         else:
             _note_fallback("conv_fprop")
-            b = _f32(bias).to(x.dtype)
+            b = None if bias is None else bias.detach().to(x.dtype)
             y = _nhwc(F.conv2d(x, w, b, stride, padding, dilation, groups))
             if want_stats:
                 stats = bn_stats(y)
@@ -239,7 +239,7 @@ class _LinearFn(torch.autograd.Function):
         if tc.gemm_supported(x, w):
             return tc.linear_fwd(x, w, _f32(bias))
         _note_fallback("linear_fwd")
-        return F.linear(x, w, _f32(bias).to(x.dtype))
+        return F.linear(x, w, None if bias is None else bias.detach().to(x.dtype))
 
     @staticmethod
     def backward(ctx, gy):

@@ -18,7 +18,7 @@ def main():
     steps = 3
     w = bootstrap.init_world("cuda")
     bs, hw = int(os.environ.get("MPB_PROF_BATCH", "256")), int(os.environ.get("MPB_PROF_IMAGE", "224"))
-    s = Settings(MODEL_NAME=model, NUM_CLASSES=1000, BATCH_SIZE=bs, HEIGHT=hw, WIDTH=hw, USE_PRETRAINED=False,
+    s = Settings(MODEL_NAME=model, NUM_CLASSES=int(os.environ.get("MPB_PROF_CLASSES", "1000")), BATCH_SIZE=bs, HEIGHT=hw, WIDTH=hw, USE_PRETRAINED=False,
                  DTYPE="bf16", LR=4e-4)
     tr = Trainer(s, w)
     batches = list(iter(tr.make_shard(total=2 * bs, shuffle=False)))
