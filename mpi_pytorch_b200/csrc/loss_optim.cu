@@ -19,30 +19,37 @@ __global__ void __launch_bounds__(256) softmax_ce_kernel(const T* __restrict__ l
   const T* x = logits + row * (long long)C;
   T* dx = dlogits + row * (long long)C;
   const int tid = threadIdx.x;
-  const bool vec = (C % 8 == 0) && ((reinterpret_cast<uintptr_t>(x) & 31) == 0);
+  // Rows need not be vector-aligned (64,500 classes: a bf16 row is 129,000 B, so odd rows start 8 B off): scalar head up
+  // to the first 8-element boundary that is 32-byte (fp32) / 16-byte (bf16) aligned, vector body, scalar tail.
+  constexpr int kVecBytes = 8 * (int)sizeof(T);
+  int head = (int)(((kVecBytes - (reinterpret_cast<uintptr_t>(x) % kVecBytes)) % kVecBytes) / sizeof(T));
+  if ((reinterpret_cast<uintptr_t>(dx) % kVecBytes) != (reinterpret_cast<uintptr_t>(x) % kVecBytes) ||
+      (reinterpret_cast<uintptr_t>(x) % sizeof(T)) != 0)
+    head = C;                                                    // differently aligned output: all scalar
+  if (head > C) head = C;
+  const int body_end = head + ((C - head) / 8) * 8;
   float m = -INFINITY, s = 0.f;
-  if (vec) {
-    for (int i = tid * 8; i < C; i += blockDim.x * 8) {
-      float v[8];
-      load8(x + i, v);
-      float lm = v[0];
+  auto scalar_stat = [&](int i) {
+    const float v = to_f(x[i]);
+    const float nm = fmaxf(m, v);
+    s = s * __expf(m - nm) + __expf(v - nm);
+    m = nm;
+  };
+  for (int i = tid; i < head; i += blockDim.x) scalar_stat(i);
+  for (int i = head + tid * 8; i < body_end; i += blockDim.x * 8) {
+    float v[8];
+    load8(x + i, v);
+    float lm = v[0];
 #pragma unroll
-      for (int k = 1; k < 8; ++k) lm = fmaxf(lm, v[k]);
-      const float nm = fmaxf(m, lm);
-      float ls = 0.f;
+    for (int k = 1; k < 8; ++k) lm = fmaxf(lm, v[k]);
+    const float nm = fmaxf(m, lm);
+    float ls = 0.f;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) ls += __expf(v[k] - nm);
-      s = s * __expf(m - nm) + ls;
-      m = nm;
-    }
-  } else {
-    for (int i = tid; i < C; i += blockDim.x) {
-      const float v = to_f(x[i]);
-      const float nm = fmaxf(m, v);
-      s = s * __expf(m - nm) + __expf(v - nm);
-      m = nm;
-    }
+    for (int k = 0; k < 8; ++k) ls += __expf(v[k] - nm);
+    s = s * __expf(m - nm) + ls;
+    m = nm;
   }
+  for (int i = body_end + tid; i < C; i += blockDim.x) scalar_stat(i);
   const float gm = block_max(m, red);
   const float contrib = (m == -INFINITY) ? 0.f : s * __expf(m - gm);
   const float gs = block_sum(contrib, red);
@@ -53,25 +60,24 @@ __global__ void __launch_bounds__(256) softmax_ce_kernel(const T* __restrict__ l
     if (row_loss) row_loss[row] = l;
     atomicAdd(loss_sum, l * inv_batch);
   }
-  if (vec) {
-    for (int i = tid * 8; i < C; i += blockDim.x * 8) {
-      float v[8];
-      load8(x + i, v);
+  auto scalar_grad = [&](int i) {
+    float p = __expf(to_f(x[i]) - gm) * inv_s;
+    if (i == t) p -= 1.f;
+    dx[i] = from_f<T>(p * inv_batch);
+  };
+  for (int i = tid; i < head; i += blockDim.x) scalar_grad(i);
+  for (int i = head + tid * 8; i < body_end; i += blockDim.x * 8) {
+    float v[8];
+    load8(x + i, v);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        float p = __expf(v[k] - gm) * inv_s;
-        if (i + k == t) p -= 1.f;
-        v[k] = p * inv_batch;
-      }
-      store8(dx + i, v);
+    for (int k = 0; k < 8; ++k) {
+      float p = __expf(v[k] - gm) * inv_s;
+      if (i + k == t) p -= 1.f;
+      v[k] = p * inv_batch;
     }
-  } else {
-    for (int i = tid; i < C; i += blockDim.x) {
-      float p = __expf(to_f(x[i]) - gm) * inv_s;
-      if (i == t) p -= 1.f;
-      dx[i] = from_f<T>(p * inv_batch);
-    }
+    store8(dx + i, v);
   }
+  for (int i = body_end + tid; i < C; i += blockDim.x) scalar_grad(i);
 }
 
 // loss_sum: 1 float (zeroed here); dlogits same dtype/shape as logits; row_loss optional [B] fp32.
