@@ -229,12 +229,21 @@ def conv2d(x, w, b, stride, padding, dilation=(1, 1), groups=1):
     return _ConvFn.apply(x, w, b, _pair(stride), _pair(padding), _pair(dilation), int(groups), False)
 
 
+def _arena_slot_ok(p) -> bool:
+    """True when ``p`` is an engine-managed parameter whose gradient is a contiguous fp32 view of the (zeroed) gradient
+    arena: the dW kernel may then add into it directly and report completion, instead of returning a tensor that
+    autograd would add with one more pass."""
+    return (p is not None and p.grad is not None and p.grad.dtype == torch.float32 and p.grad.dim() == 2
+            and p.grad.is_contiguous())
+
+
 class _LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias):
         w = _compute_weight(weight, x.dtype)
         ctx.save_for_backward(x, w)
         ctx.conf = (bias is not None, weight.dtype)
+        ctx.weight_param = weight if getattr(weight, "_mpb_grad_ready", None) is not None else None
         tc = _gemm()
         if tc.gemm_supported(x, w):
             return tc.linear_fwd(x, w, _f32(bias))
@@ -252,7 +261,12 @@ class _LinearFn(torch.autograd.Function):
             if ctx.needs_input_grad[0]:
                 gx = tc.linear_dx(gy, w)
             if ctx.needs_input_grad[1]:
-                gw = tc.linear_dw(gy, x).to(wdtype)
+                wp = ctx.weight_param
+                if _arena_slot_ok(wp):
+                    tc.linear_dw(gy, x, out=wp.grad)            # += the weight's slot of the gradient arena
+                    wp._mpb_grad_ready(wp)
+                else:
+                    gw = tc.linear_dw(gy, x).to(wdtype)
         else:
             _note_fallback("linear_bwd")
             if ctx.needs_input_grad[0]:
@@ -286,6 +300,7 @@ class _LinearPadFn(torch.autograd.Function):
             bp[:n].copy_(bias.detach())
         ctx.save_for_backward(x, wp)
         ctx.conf = (bias is not None, weight.dtype, n)
+        ctx.weight_param = weight if getattr(weight, "_mpb_grad_ready", None) is not None else None
         return _gemm().linear_fwd(x, wp, bp)[:, :n]
 
     @staticmethod
@@ -296,7 +311,14 @@ class _LinearPadFn(torch.autograd.Function):
         gp = torch.zeros((gy.shape[0], wp.shape[0]), dtype=x.dtype, device=x.device)
         gp[:, :n].copy_(gy)
         gx = tc.linear_dx(gp, wp) if ctx.needs_input_grad[0] else None
-        gw = tc.linear_dw(gp, x)[:n].to(wdtype) if ctx.needs_input_grad[1] else None
+        gw = None
+        if ctx.needs_input_grad[1]:
+            wparam = ctx.weight_param
+            if _arena_slot_ok(wparam):
+                tc.linear_dw(gp, x, out=wparam.grad, rows=n)      # only the n real rows are written
+                wparam._mpb_grad_ready(wparam)
+            else:
+                gw = tc.linear_dw(gp, x)[:n].to(wdtype)
         gb = gy.float().sum(dim=0) if (has_bias and ctx.needs_input_grad[2]) else None
         return gx, gw, gb
 

@@ -39,10 +39,14 @@ def _check(rc: int, what: str) -> None:
 # ----------------------------------------------------------------------------------------------- GEMM
 def gemm(a: torch.Tensor, b: torch.Tensor, m: int, n: int, k: int, a_mn: bool, b_mn: bool,
          bias: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16, splitk: int = 1,
-         stats: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """D[m,n] = A[m,k] @ B[n,k]^T.  ``a`` is stored [m][k] (a_mn False) or [k][m] (True); same for ``b``."""
+         stats: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """D[m,n] = A[m,k] @ B[n,k]^T.  ``a`` is stored [m][k] (a_mn False) or [k][m] (True); same for ``b``.
+    ``out`` (fp32 [m,n], contiguous): the product is ADDED to it (fp32 RED) -- a slot of the gradient arena."""
     assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.is_contiguous() and b.is_contiguous()
-    if splitk > 1:
+    if out is not None:
+        assert out.dtype == torch.float32 and out.is_contiguous() and tuple(out.shape) == (m, n)
+        d, mode = out, 2
+    elif splitk > 1:
         d = torch.zeros((m, n), dtype=torch.float32, device=a.device)
         mode = 2
     else:
@@ -68,11 +72,21 @@ def linear_fwd(x, w, bias):
 
 
 def linear_dx(gy, w):
-    return gemm(gy, w, gy.shape[0], w.shape[1], w.shape[0], False, True)
+    """dX[M, in] = gy[M, out] @ W[out, in].  A wide head (64,500 classes) makes this a long reduction over very few
+    output tiles (128 x 512 -> 4 CTAs, 1,008 k-blocks each): split K across CTAs so the GPU is filled."""
+    m, n, k = gy.shape[0], w.shape[1], w.shape[0]
+    tiles = ((m + 127) // 128) * ((n + 127) // 128)
+    splitk = 1
+    if tiles < 74 and k >= 4096:
+        splitk = max(1, min(k // 512, 296 // tiles))
+    return gemm(gy, w, m, n, k, False, True, splitk=splitk)
 
 
-def linear_dw(gy, x):
-    return gemm(gy, x, gy.shape[1], x.shape[1], gy.shape[0], True, True, out_dtype=torch.float32)
+def linear_dw(gy, x, out=None, rows=None):
+    """dW[out, in] = gy^T x (fp32).  ``out``: accumulate into that fp32 buffer (the weight's slot of the gradient
+    arena); ``rows``: number of valid output rows when gy carries zero-padded columns."""
+    m = gy.shape[1] if rows is None else rows
+    return gemm(gy, x, m, x.shape[1], gy.shape[0], True, True, out_dtype=torch.float32, out=out)
 
 
 # ----------------------------------------------------------------------------------------------- conv
