@@ -80,6 +80,10 @@ int mpb_adaptive_avgpool(const void* in, void* out, int N, int H, int W, int C, 
                          int dtype, void* stream);
 int mpb_relu_fwd(const void* x, void* y, long long n, int dtype, void* stream);
 int mpb_relu_bwd(const void* dy, const void* y, void* dx, long long n, int dtype, void* stream);
+/* dx = dy * (y > 0) and sums[0:C] += column sums of dx in one pass (sums: 2*C zeroed floats): the backward of a
+ * Conv2d(+bias) -> ReLU pair, where the column sums are the bias gradient (models.py:47-72 stacks).           */
+int mpb_relu_bwd_colsum(const void* dy, const void* y, void* dx, float* sums, long long M, int C, int dtype,
+                        void* stream);
 int mpb_dropout(const void* x, void* y, long long n, unsigned int seed, float p, int dtype, void* stream);
 /* M rows of row_bytes (multiple of 16) between row-pitched buffers: channel concat into an NHWC slice and its inverse
  * (torch.cat of the DenseNet / Inception / Fire blocks, models.py:56-87).                                       */

@@ -385,6 +385,44 @@ MPB_API int mpb_bn_relu_bwd_recompute_ex(const void* dz, const void* x, const fl
   return 0;
 }
 
+// ReLU backward fused with the per-channel column sum of its result: dx = dy * (y > 0), sums[c] += sum_m dx[m][c].
+// For a Conv2d(+bias) -> ReLU pair (VGG / AlexNet / SqueezeNet, models.py:47-72) dx is the convolution's output
+// gradient and its column sums are the bias gradient, so one pass replaces relu_bwd + a separate reduction over dx.
+// sums: 2*C floats, zeroed by the caller (the second half is scratch of the shared reduction helper).
+namespace {
+template <typename T>
+__global__ void __launch_bounds__(256) relu_bwd_colsum_kernel(const T* __restrict__ dy, const T* __restrict__ y,
+                                                              T* __restrict__ dx, float* __restrict__ sums, long long M,
+                                                              int C, int cvecs, int rows_per_block) {
+  extern __shared__ float smem[];
+  const int cv = threadIdx.x % cvecs, r = threadIdx.x / cvecs;
+  float s[8] = {0}, z[8] = {0};
+  for (long long m = (long long)blockIdx.x * rows_per_block + r; m < M; m += (long long)gridDim.x * rows_per_block) {
+    float g[8], v[8];
+    load8(dy + m * C + cv * 8, g);
+    load8(y + m * C + cv * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { g[k] = v[k] > 0.f ? g[k] : 0.f; s[k] += g[k]; }
+    store8(dx + m * C + cv * 8, g);
+  }
+  reduce_pair_to_global(s, z, sums, sums + C, cvecs, rows_per_block, smem);
+}
+}  // namespace
+
+MPB_API int mpb_relu_bwd_colsum(const void* dy, const void* y, void* dx, float* sums, long long M, int C, int dtype,
+                                void* stream) {
+  if (C <= 0 || C % 8 != 0 || C > 2048) return -1;
+  if (M <= 0) return 0;
+  const Map mp = make_map(C);
+  const size_t smem = (size_t)mp.threads * 16 * sizeof(float);
+  const int g = rows_grid(M, mp.rows_per_block, 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  DISPATCH_T(dtype, relu_bwd_colsum_kernel<T><<<g, mp.threads, smem, st>>>((const T*)dy, (const T*)y, (T*)dx, sums, M, C,
+                                                                             mp.cvecs, mp.rows_per_block);)
+  MPB_CHECK_LAUNCH();
+  return 0;
+}
+
 MPB_API int mpb_bn_relu_bwd_recompute(const void* dz, const void* x, const float* gamma, const float* beta,
                                       const float* save_mean, const float* save_invstd, float* dsum, void* dx,
                                       float* dgamma, float* dbeta, long long M, int C, int dtype, void* stream) {

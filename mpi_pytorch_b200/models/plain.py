@@ -18,6 +18,27 @@ from .layers import AdaptiveAvgPool2d, BatchNorm2d, Conv2d, Dropout, Linear, Max
 
 
 # ---------------------------------------------------------------------------- AlexNet
+def run_stack(features: nn.Sequential, x: torch.Tensor) -> torch.Tensor:
+    """Run a torchvision-style ``features`` stack, fusing Conv -> BN -> ReLU triples (statistics and activation in
+    the conv / BN kernels) and Conv -> ReLU pairs (activation in the conv epilogue, mask + bias gradient in one
+    backward pass) where the stack has them.  Module indices -- and so state_dict names -- are untouched."""
+    mods = list(features)
+    i = 0
+    while i < len(mods):
+        m = mods[i]
+        if isinstance(m, Conv2d) and i + 2 < len(mods) and isinstance(mods[i + 1], BatchNorm2d) \
+                and isinstance(mods[i + 2], ReLU):
+            x = ops.conv_bn_act(x, m, mods[i + 1], relu=True)
+            i += 3
+        elif isinstance(m, Conv2d) and i + 1 < len(mods) and isinstance(mods[i + 1], ReLU):
+            x = ops.conv_relu(x, m)
+            i += 2
+        else:
+            x = m(x)
+            i += 1
+    return x
+
+
 class AlexNet(nn.Module):
     def __init__(self, num_classes: int = 1000, dropout: float = 0.5):
         super().__init__()
@@ -36,7 +57,7 @@ class AlexNet(nn.Module):
         )
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = self.avgpool(self.features(x))
+        x = self.avgpool(run_stack(self.features, x))
         return self.classifier(torch.flatten(x, 1))
 
 
@@ -85,18 +106,7 @@ class VGG(nn.Module):
                 init.constant_(m.bias, 0)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        mods = list(self.features)
-        i = 0
-        while i < len(mods):
-            m = mods[i]
-            # fuse Conv -> BN -> ReLU triples / BN -> ReLU pairs where the stack has them
-            if isinstance(m, Conv2d) and i + 2 < len(mods) and isinstance(mods[i + 1], BatchNorm2d) \
-                    and isinstance(mods[i + 2], ReLU):
-                x = ops.conv_bn_act(x, m, mods[i + 1], relu=True)
-                i += 3
-            else:
-                x = m(x)
-                i += 1
+        x = run_stack(self.features, x)
         x = self.avgpool(x)
         return self.classifier(torch.flatten(x, 1))
 

@@ -66,6 +66,13 @@ def conv_bn_act(x, conv, bn, relu=True, residual=None):
     return ref.batch_norm_act(y, bn, residual, relu)
 
 
+def conv_relu(x, conv):
+    """Conv2d followed by ReLU (VGG / AlexNet / SqueezeNet stacks, /root/reference/models.py:47-72)."""
+    if _nat(x):
+        return native().conv_relu(x, conv)
+    return ref.relu(ref.conv2d(x, conv.weight, conv.bias, conv.stride, conv.padding, conv.dilation, conv.groups))
+
+
 def relu(x, inplace=False):
     if _nat(x):
         return native().relu(x, inplace)

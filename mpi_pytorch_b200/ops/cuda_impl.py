@@ -135,23 +135,26 @@ def _gemm():
 
 class _ConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, padding, dilation, groups, want_stats):
+    def forward(ctx, x, weight, bias, stride, padding, dilation, groups, want_stats, relu=False):
         # the (non-differentiable) statistics output would otherwise get a materialised zeros gradient: one tiny
         # fill launch per convolution per step
         ctx.set_materialize_grads(False)
         x = _nhwc(x)
         w = _compute_weight(weight, x.dtype)
-        ctx.save_for_backward(x, w)
         ctx.conf = (stride, padding, dilation, groups, bias is not None, weight.dtype)
         ctx.weight_param = weight if getattr(weight, "_mpb_grad_ready", None) is not None else None
         tc = _gemm()
         stats = None
         ctx.xcol = None
         ctx.xs2d = None
+        fused_relu = False
         if tc.stem_s2d_ok(x, w, stride, padding, dilation, groups):
             y, stats, ctx.xs2d = tc.conv_fprop_stem(x, w, _f32(bias), padding, want_stats)
         elif tc.fprop_ok(x, w, stride, padding, dilation, groups):
-            y, stats = tc.conv_fprop(x, w, _f32(bias), stride, padding, want_stats)
+            # Conv2d -> ReLU pairs: the activation runs in the conv epilogue (statistics, when wanted, are of the
+            # pre-activation values, so the two are never combined)
+            y, stats = tc.conv_fprop(x, w, _f32(bias), stride, padding, want_stats, relu=relu and not want_stats)
+            fused_relu = relu and not want_stats
         elif tc.im2col_ok(x, w, stride, padding, dilation, groups):
             y, stats, ctx.xcol = tc.conv_fprop_im2col(x, w, _f32(bias), stride, padding,
                                                       want_stats)
@@ -161,6 +164,12 @@ class _ConvFn(torch.autograd.Function):
             y = _nhwc(F.conv2d(x, w, b, stride, padding, dilation, groups))
             if want_stats:
                 stats = bn_stats(y)
+        if relu:
+            if not fused_relu:
+                _call("mpb_relu_fwd", _p(y), _p(y), c_ll(y.numel()), c_int(_dt(y)), c_void_p(_stream()))   # in place
+            ctx.save_for_backward(x, w, y)   # y is the mask source of the ReLU backward
+        else:
+            ctx.save_for_backward(x, w)
         ctx.mark_non_differentiable(*([stats] if stats is not None else []))
         if want_stats:
             return y, stats
@@ -169,10 +178,24 @@ class _ConvFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, gy, *unused):
         if gy is None:
-            return (None,) * 8
-        x, w = ctx.saved_tensors
+            return (None,) * 9
+        saved = ctx.saved_tensors
+        x, w = saved[0], saved[1]
         stride, padding, dilation, groups, has_bias, wdtype = ctx.conf
         gy = _nhwc(gy)
+        gb_fused = None
+        if len(saved) > 2:
+            # ReLU backward; for a biased conv the same pass also produces the bias gradient (column sums of dy)
+            yo, k = saved[2], gy.shape[1]
+            dy = torch.empty_like(gy)
+            if has_bias and ctx.needs_input_grad[2] and k % 8 == 0 and k <= 2048:
+                sums = _scratch.take(2 * k, gy.device)[0]
+                _call("mpb_relu_bwd_colsum", _p(gy), _p(yo), _p(dy), _p(sums), c_ll(gy.numel() // k), c_int(k),
+                      c_int(_dt(gy)), c_void_p(_stream()))
+                gb_fused = sums[:k]
+            else:
+                _call("mpb_relu_bwd", _p(gy), _p(yo), _p(dy), c_ll(gy.numel()), c_int(_dt(gy)), c_void_p(_stream()))
+            gy = dy
         need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         tc = _gemm()
         gx = gw = gb = None
@@ -216,17 +239,27 @@ class _ConvFn(torch.autograd.Function):
                 gw = fw.to(wdtype)
         if has_bias and ctx.needs_input_grad[2]:
             k = gy.shape[1]
-            if k % 8 == 0 and k <= 2048 and gy.dtype in (torch.bfloat16, torch.float32):
+            if gb_fused is not None:
+                gb = gb_fused
+            elif k % 8 == 0 and k <= 2048 and gy.dtype in (torch.bfloat16, torch.float32):
                 gb = bn_stats(gy)[:k]             # one pass over dy in its own dtype (no fp32 copy + library reduction)
             else:
                 gb = gy.float().sum(dim=(0, 2, 3))
-        return gx, gw, gb, None, None, None, None, None
+        return gx, gw, gb, None, None, None, None, None, None
 
 
 def conv2d(x, w, b, stride, padding, dilation=(1, 1), groups=1):
     if x.dtype not in (torch.bfloat16, torch.float32):
         return F.conv2d(x, w, b, stride, padding, dilation, groups)
     return _ConvFn.apply(x, w, b, _pair(stride), _pair(padding), _pair(dilation), int(groups), False)
+
+
+def conv_relu(x, conv):
+    """Conv2d -> ReLU as one unit: activation in the conv epilogue, mask + bias gradient in one backward pass."""
+    if x.dtype != torch.bfloat16 or x.dim() != 4:
+        return relu(conv2d(x, conv.weight, conv.bias, conv.stride, conv.padding, conv.dilation, conv.groups))
+    return _ConvFn.apply(x, conv.weight, conv.bias, _pair(conv.stride), _pair(conv.padding), _pair(conv.dilation),
+                         int(conv.groups), False, True)
 
 
 def _arena_slot_ok(p) -> bool:
