@@ -51,6 +51,71 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const T* __restrict__ 
   }
 }
 
+// 2x2 / stride 2 / no padding (every VGG stage, models.py:56-63): windows do not overlap, so one thread owns one output
+// vector and its 2x2 input quad -- four independent 16-byte loads (forward) or stores (backward) in flight, one index
+// decomposition per quad instead of one per input pixel.  Argmax positions are r*2+s like the generic kernel's.
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool2x2_fwd_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                             unsigned char* __restrict__ idx, PoolGeom g) {
+  const int cvecs = g.C / 8;
+  const long long total = (long long)g.N * g.Ho * g.Wo * cvecs;
+  const long long row = (long long)g.W * g.C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const unsigned iu = (unsigned)i;
+    const int cv = (int)(iu % (unsigned)cvecs);
+    unsigned t = iu / (unsigned)cvecs;
+    const int wo = (int)(t % (unsigned)g.Wo); t /= (unsigned)g.Wo;
+    const int ho = (int)(t % (unsigned)g.Ho);
+    const int n = (int)(t / (unsigned)g.Ho);
+    const T* p = x + (((long long)n * g.H + 2 * ho) * g.W + 2 * wo) * g.C + cv * 8;
+    float v[4][8];
+    load8(p, v[0]); load8(p + g.C, v[1]); load8(p + row, v[2]); load8(p + row + g.C, v[3]);
+    float m[8];
+    uint2 pk = make_uint2(0u, 0u);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float best = v[0][k];
+      unsigned pos = 0;
+#pragma unroll
+      for (int q = 1; q < 4; ++q)
+        if (v[q][k] > best || v[q][k] != v[q][k]) { best = v[q][k]; pos = q; }     // first maximum wins; NaN propagates
+      m[k] = best;
+      if (k < 4) pk.x |= pos << (8 * k); else pk.y |= pos << (8 * (k - 4));
+    }
+    const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
+    store8(y + o, m);
+    if (idx) *reinterpret_cast<uint2*>(idx + o) = pk;
+  }
+}
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool2x2_bwd_kernel(const T* __restrict__ dy, const unsigned char* __restrict__ idx,
+                                                             T* __restrict__ dx, PoolGeom g) {
+  const int cvecs = g.C / 8;
+  const long long total = (long long)g.N * g.Ho * g.Wo * cvecs;
+  const long long row = (long long)g.W * g.C;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const unsigned iu = (unsigned)i;
+    const int cv = (int)(iu % (unsigned)cvecs);
+    unsigned t = iu / (unsigned)cvecs;
+    const int wo = (int)(t % (unsigned)g.Wo); t /= (unsigned)g.Wo;
+    const int ho = (int)(t % (unsigned)g.Ho);
+    const int n = (int)(t / (unsigned)g.Ho);
+    const long long o = (((long long)n * g.Ho + ho) * g.Wo + wo) * g.C + cv * 8;
+    const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
+    float gv[8];
+    load8(dy + o, gv);
+    float out[4][8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const unsigned pos = ((k < 4 ? pk.x : pk.y) >> (8 * (k & 3))) & 0xFFu;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) out[q][k] = (pos == (unsigned)q) ? gv[k] : 0.f;
+    }
+    T* p = dx + (((long long)n * g.H + 2 * ho) * g.W + 2 * wo) * g.C + cv * 8;
+    store8(p, out[0]); store8(p + g.C, out[1]); store8(p + row, out[2]); store8(p + row + g.C, out[3]);
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ dy, const unsigned char* __restrict__ idx,
                                                           T* __restrict__ dx, PoolGeom g) {
@@ -566,6 +631,9 @@ MPB_API int mpb_maxpool_fwd(const void* x, void* y, unsigned char* idx, int N, i
     } else {
       maxpool3x3_fwd_kernel<float><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const float*)x, (float*)y, idx, g);
     }
+  } else if (kh == 2 && kw == 2 && sh == 2 && sw == 2 && ph == 0 && pw == 0 && H % 2 == 0 && W % 2 == 0 && Ho == H / 2 &&
+             Wo == W / 2) {
+    DISPATCH_T(dtype, maxpool2x2_fwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, g);)
   } else {
     DISPATCH_T(dtype, maxpool_fwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, g);)
   }
@@ -581,6 +649,10 @@ MPB_API int mpb_maxpool_bwd(const void* dy, const unsigned char* idx, void* dx, 
       Wo == W / 2) {
     const long long quads = (long long)N * Ho * Wo * (C / 8);
     DISPATCH_T(dtype, maxpool3x3s2_bwd_kernel<T><<<grid_for(quads, 256), 256, 0, (cudaStream_t)stream>>>((const T*)dy, idx, (T*)dx, g);)
+  } else if (kh == 2 && kw == 2 && sh == 2 && sw == 2 && ph == 0 && pw == 0 && H % 2 == 0 && W % 2 == 0 && Ho == H / 2 &&
+             Wo == W / 2) {
+    const long long outs = (long long)N * Ho * Wo * (C / 8);
+    DISPATCH_T(dtype, maxpool2x2_bwd_kernel<T><<<grid_for(outs, 256), 256, 0, (cudaStream_t)stream>>>((const T*)dy, idx, (T*)dx, g);)
   } else {
     DISPATCH_T(dtype, maxpool_bwd_kernel<T><<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>((const T*)dy, idx, (T*)dx, g);)
   }
