@@ -714,7 +714,7 @@ def run_pipeline(args) -> None:
     # ---- phase 2: the staged pipeline over all ranks
     def model_fn():
         m, _ = initialize_model("resnet18", classes, feature_extract=False, use_pretrained=False)
-        m.load_state_dict(torch.load(checkpoint_path(ckdir, "resnet18"), map_location="cpu", weights_only=False)["state_dict"])
+        m.load_state_dict(torch.load(checkpoint_path(ckdir, "resnet18"), map_location="cpu", weights_only=True)["state_dict"])
         if cuda:
             m = ops.prepare_inference(m.to(dev).to(memory_format=torch.channels_last), torch.bfloat16)
         return m

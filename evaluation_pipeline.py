@@ -62,7 +62,7 @@ def pipeline(world=None, settings=None, n_samples=None):
                                     feature_extract=False)
         path = checkpoint_path(settings.CHECKPOINT_DIR, settings.MODEL_NAME)
         if os.path.exists(path):
-            model.load_state_dict(torch.load(path, map_location='cpu', weights_only=False)['state_dict'])
+            model.load_state_dict(torch.load(path, map_location='cpu', weights_only=True)['state_dict'])
         else:
             logger.warning('no checkpoint at {}: predicting with random weights'.format(path))
         if world.device.type == 'cuda':

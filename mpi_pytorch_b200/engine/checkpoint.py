@@ -65,7 +65,10 @@ def save_checkpoint(state: Dict[str, Any], epoch: int, model_name: str, checkpoi
 def load_checkpoint(checkpoint_fpath: str, model: torch.nn.Module, optimizer: Any = None,
                     map_location: Any = "cpu") -> Tuple[torch.nn.Module, Any, int]:
     """Same signature / return value as helpers.py:10-15."""
-    ck = torch.load(checkpoint_fpath, map_location=map_location, weights_only=False)
+    # tensors, numbers, strings, dicts and lists only -- which is all the checkpoint contract contains -- so the file is
+    # read with the restricted unpickler; MPB_TRUST_CHECKPOINT=1 allows arbitrary pickles (files you wrote yourself)
+    trust = os.environ.get("MPB_TRUST_CHECKPOINT", "0") == "1"
+    ck = torch.load(checkpoint_fpath, map_location=map_location, weights_only=not trust)
     model.load_state_dict(ck["state_dict"])
     if optimizer is not None and ck.get("optimizer") is not None:
         optimizer.load_state_dict(ck["optimizer"])
