@@ -64,3 +64,34 @@ def test_row_view_recognises_channel_slices_of_nhwc_tensors():
     assert row_view(big[:, :, 1:4]) is None                              # a spatial crop is not a row view
     assert row_view(torch.randn(2, 160, 5, 6)) is None                   # NCHW-contiguous
     assert row_view(torch.randn(4, 8)) is None
+
+
+def test_measured_algo_table_lookup():
+    """parallel/algo_table.json (written by scripts/peer_sweep.py) drives the per-bucket algorithm / grid choice."""
+    from mpi_pytorch_b200.parallel.peer import load_algo_table, table_choice
+    table = load_algo_table()
+    assert set(table) >= {2, 4, 8}
+    for w, rows in table.items():
+        assert rows == sorted(rows, key=lambda r: r[0]) and all(a in ("oneshot", "twoshot", "nvls") and 1 <= g <= 64
+                                                                for _, a, g in rows)
+    assert table_choice(table, 8, 32 << 20, True) == ("nvls", 16)          # the measured optimum at W = 8
+    assert table_choice(table, 8, 32 << 20, False)[0] == "twoshot"         # no multicast on this host: same grid, peer loads
+    assert table_choice(table, 8, 4 << 30, True) is not None               # beyond the last row: the last row applies
+    assert table_choice(table, 3, 1 << 20, True) is None                   # unmeasured world size: fixed crossover
+    assert table_choice({}, 8, 1 << 20, True) is None
+
+
+def test_conv_relu_pairs_are_fused_without_changing_the_model():
+    """run_stack fuses Conv->ReLU pairs of the VGG / AlexNet feature stacks; outputs and parameter names are unchanged."""
+    import torch
+    from mpi_pytorch_b200.models import initialize_model
+    for name in ("vgg16", "alexnet"):
+        torch.manual_seed(0)
+        m, _ = initialize_model(name, 7, False, use_pretrained=False)
+        m.eval()
+        x = torch.randn(2, 3, 64, 64)
+        with torch.no_grad():
+            want = m.classifier(torch.flatten(m.avgpool(m.features(x)), 1))     # the plain nn.Sequential walk
+            got = m(x)
+        assert torch.allclose(got, want, atol=1e-5)
+        assert any(k.startswith("features.0.weight") for k in m.state_dict())
