@@ -187,7 +187,7 @@ class PeerCollectives:
                 raise RuntimeError("mpb_vmm_import(rank {}) failed: {}".format(r, rc))
             peers.append(int(p.value))
         for r, f in enumerate(fds):
-            if f >= 0 and (r != self.rank or True):
+            if f >= 0:                                   # every received descriptor, our own duplicate included
                 try:
                     os.close(f)
                 except OSError:
