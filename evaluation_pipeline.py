@@ -38,13 +38,13 @@ def build_sources(settings, world, n):
         render_index_images(df, settings.TEST_DIR)       # stand-in JPEGs for generated rows; no-op for Herbarium
     ds = GetData(settings.TEST_DIR, df['file_name'].values, df['category_id'].values, None, mode='test')
     hmax, wmax = int(df['height'].max()), int(df['width'].max())
-    frame_hw = torch.as_tensor(df[['height', 'width']].values)
+    frame_hw = torch.as_tensor(df[['height', 'width']].values.copy())
 
     def source(i0, i1):
         # a list of frames of their own sizes: stage 1 resizes each image over its true extent, as
         # pil_image.resize does in the reference (evaluation_pipeline.py:89), not over a padded canvas
         return [ds.load_uint8(i) for i in range(i0, i1)]
-    return source, torch.as_tensor(df['category_id'].values), (hmax, wmax), frame_hw
+    return source, torch.as_tensor(df['category_id'].values.copy()), (hmax, wmax), frame_hw
 
 
 def pipeline(world=None, settings=None, n_samples=None):
